@@ -1,0 +1,610 @@
+// rt_b200.cu -- C-ABI implementation (include/rt_b200.h) of the B200-native `src/spheres` hot path.
+// Host side: scene recorder (the reference's constructors, flattened), camera basis, Halton tables,
+// launch logic.  Device side: rt_kernels.cuh.  No CPU fallback exists: every compute entry point
+// launches a CUDA kernel or fails with RT_ERR_CUDA.
+//
+// Build (see cpuraytracer_b200/build.py):
+//   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -fmad=false -Xcompiler -fPIC,-ffp-contract=off
+//        -shared -o librt_b200.so rt_b200.cu
+#include "../../include/rt_b200.h"
+#include "rt_kernels.cuh"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+using rt::u64;
+
+// ------------------------------------------------------------------------------------------------
+// errors
+// ------------------------------------------------------------------------------------------------
+static thread_local std::string g_last_error;
+static int fail(int code, const char* fmt, ...) {
+    char buf[1024];
+    va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof buf, fmt, ap); va_end(ap);
+    g_last_error = buf;
+    return code;
+}
+#define RT_CUDA(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) \
+    return fail(e_ == cudaErrorMemoryAllocation ? RT_ERR_OUT_OF_MEMORY : RT_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e_), __FILE__, __LINE__); } while (0)
+
+// ------------------------------------------------------------------------------------------------
+// host restatement of the scene-building arithmetic (runs once per scene/camera, not per sample)
+// ------------------------------------------------------------------------------------------------
+namespace host {
+struct V3 { float x, y, z; };
+static inline V3 sub(V3 a, V3 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
+static inline V3 add(V3 a, V3 b) { return {a.x + b.x, a.y + b.y, a.z + b.z}; }
+static inline V3 scale(float s, V3 a) { return {s * a.x, s * a.y, s * a.z}; }
+static inline float dot3(V3 a, V3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }          // XMVector3Dot, SSE2 order
+static inline V3 cross3(V3 a, V3 b) { return {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x}; }
+static inline V3 normalize3(V3 v) {                                                           // XMVector3Normalize
+    const float l2 = dot3(v, v), l = std::sqrt(l2);
+    if (l == 0.f) return {0.f, 0.f, 0.f};
+    if (std::isinf(l2)) { const float q = std::nanf(""); return {q, q, q}; }
+    return {v.x / l, v.y / l, v.z / l};
+}
+// XMCOLOR(float,float,float,float): saturate, *255, round-to-nearest-even (XMStoreColor); XMLoadColor: k * (1/255)
+static inline float xmcolor_roundtrip(float x) {
+    float v = std::fmin(std::fmax(x, 0.0f), 1.0f);
+    v = v * 255.0f;
+    const int k = static_cast<int>(std::nearbyint(v));
+    return static_cast<float>(k) * (1.0f / 255.0f);
+}
+// Random::HaltonSample, quasi-random.cpp:3-16
+static inline float halton(uint64_t index, uint32_t base) {
+    float result = 0.f, f = 1.f;
+    const float fb = static_cast<float>(base);
+    while (index > 0) {
+        f = f / fb;
+        result += f * static_cast<float>(index % base);
+        index = index / base;
+    }
+    return result;
+}
+// Camera::Camera, camera.cpp:3-28
+static void camera_basis(const rt_camera_params& p, rt_camera_basis& c) {
+    const V3 origin{p.origin[0], p.origin[1], p.origin[2]}, look{p.look_at[0], p.look_at[1], p.look_at[2]};
+    const float theta = p.vfov_deg * 3.141592654f / 180.f;
+    const float half_h = std::tan(theta / 2.f);
+    const float half_w = p.aspect * half_h;
+    const V3 up{0.f, 1.f, 0.f};
+    const V3 w = normalize3(sub(look, origin));
+    const V3 u = normalize3(cross3(up, w));
+    const V3 v = cross3(w, u);
+    const V3 io = add(origin, scale(1.f, w)), mx = scale(half_w, u), my = scale(half_h, v);
+    c.origin[0] = origin.x; c.origin[1] = origin.y; c.origin[2] = origin.z;
+    c.image_origin[0] = io.x; c.image_origin[1] = io.y; c.image_origin[2] = io.z;
+    c.x[0] = mx.x; c.x[1] = mx.y; c.x[2] = mx.z;
+    c.y[0] = my.x; c.y[1] = my.y; c.y[2] = my.z;
+    c.aperture = p.aperture; c.focus = p.focus;
+}
+}  // namespace host
+
+// ------------------------------------------------------------------------------------------------
+// scene recorder
+// ------------------------------------------------------------------------------------------------
+struct rt_scene {
+    std::vector<rt_sphere_desc> spheres;
+    std::vector<rt_material_desc> materials;
+    std::vector<rt_texture_desc> textures;
+    std::vector<rt_light_desc> lights;
+    float sky_luminance = 0.f;
+    int32_t sky_texture = -1;
+};
+
+static bool finite3(const float* v) { return std::isfinite(v[0]) && std::isfinite(v[1]) && std::isfinite(v[2]); }
+
+extern "C" {
+
+const char* rt_last_error(void) { return g_last_error.c_str(); }
+const char* rt_build_info(void) {
+    return "cpuraytracer_b200 librt_b200: sm_100a megakernel (FFMA2 conservative cull + exact reference-order tests), "
+           "nvcc " __DATE__ ", -fmad=false";
+}
+
+int rt_scene_create(rt_scene** out) {
+    if (!out) return fail(RT_ERR_INVALID_ARGUMENT, "rt_scene_create: out is NULL");
+    *out = new rt_scene();
+    return RT_OK;
+}
+void rt_scene_destroy(rt_scene* s) { delete s; }
+
+int rt_scene_add_texture_const(rt_scene* s, const float rgba[4]) {
+    if (!s || !rgba) return -fail(RT_ERR_INVALID_ARGUMENT, "rt_scene_add_texture_const: NULL argument");
+    rt_texture_desc t{}; t.kind = RT_TEX_CONST; t.tiling = 0.f;
+    for (int k = 0; k < 4; ++k) { t.c0[k] = host::xmcolor_roundtrip(rgba[k]); t.c1[k] = t.c0[k]; }
+    s->textures.push_back(t);
+    return static_cast<int>(s->textures.size()) - 1;
+}
+int rt_scene_add_texture_checker(rt_scene* s, const float rgba0[4], const float rgba1[4], float tiling) {
+    if (!s || !rgba0 || !rgba1) return -fail(RT_ERR_INVALID_ARGUMENT, "rt_scene_add_texture_checker: NULL argument");
+    rt_texture_desc t{}; t.kind = RT_TEX_CHECKER; t.tiling = tiling;
+    for (int k = 0; k < 4; ++k) { t.c0[k] = host::xmcolor_roundtrip(rgba0[k]); t.c1[k] = host::xmcolor_roundtrip(rgba1[k]); }
+    s->textures.push_back(t);
+    return static_cast<int>(s->textures.size()) - 1;
+}
+static int add_material(rt_scene* s, int kind, int texture, float smoothness, float ior, const char* who) {
+    if (!s) return -fail(RT_ERR_INVALID_ARGUMENT, "%s: scene is NULL", who);
+    if (kind != RT_MAT_TRANSPARENT && (texture < 0 || texture >= static_cast<int>(s->textures.size())))
+        return -fail(RT_ERR_INVALID_ARGUMENT, "%s: texture id %d out of range [0,%zu)", who, texture, s->textures.size());
+    rt_material_desc m{}; m.kind = kind; m.texture = kind == RT_MAT_TRANSPARENT ? -1 : texture; m.smoothness = smoothness; m.ior = ior;
+    s->materials.push_back(m);
+    return static_cast<int>(s->materials.size()) - 1;
+}
+int rt_scene_add_material_opaque(rt_scene* s, int texture, float smoothness) { return add_material(s, RT_MAT_OPAQUE, texture, smoothness, 0.f, "rt_scene_add_material_opaque"); }
+int rt_scene_add_material_metal(rt_scene* s, int texture, float smoothness) { return add_material(s, RT_MAT_METAL, texture, smoothness, 0.f, "rt_scene_add_material_metal"); }
+int rt_scene_add_material_transparent(rt_scene* s, float smoothness, float ior) {
+    if (!(ior > 0.f)) return -fail(RT_ERR_INVALID_ARGUMENT, "rt_scene_add_material_transparent: ior must be > 0");
+    return add_material(s, RT_MAT_TRANSPARENT, -1, smoothness, ior, "rt_scene_add_material_transparent");
+}
+int rt_scene_add_sphere(rt_scene* s, const float center[3], float radius, int material) {
+    if (!s || !center) return -fail(RT_ERR_INVALID_ARGUMENT, "rt_scene_add_sphere: NULL argument");
+    if (!finite3(center) || !(radius > 0.f) || !std::isfinite(radius)) return -fail(RT_ERR_INVALID_ARGUMENT, "rt_scene_add_sphere: centre must be finite and radius > 0");
+    if (material < 0 || material >= static_cast<int>(s->materials.size()))
+        return -fail(RT_ERR_INVALID_ARGUMENT, "rt_scene_add_sphere: material id %d out of range [0,%zu)", material, s->materials.size());
+    s->spheres.push_back(rt_sphere_desc{center[0], center[1], center[2], radius, material});
+    return static_cast<int>(s->spheres.size()) - 1;
+}
+int rt_scene_set_sky(rt_scene* s, float luminance, int texture) {
+    if (!s) return fail(RT_ERR_INVALID_ARGUMENT, "rt_scene_set_sky: scene is NULL");
+    if (texture < 0 || texture >= static_cast<int>(s->textures.size())) return fail(RT_ERR_INVALID_ARGUMENT, "rt_scene_set_sky: texture id %d out of range", texture);
+    s->sky_luminance = luminance; s->sky_texture = texture;
+    return RT_OK;
+}
+int rt_scene_add_directional_light(rt_scene* s, const float dir[3], const float rgba[4], float luminance) {
+    if (!s || !dir || !rgba) return fail(RT_ERR_INVALID_ARGUMENT, "rt_scene_add_directional_light: NULL argument");
+    const host::V3 n = host::normalize3({dir[0], dir[1], dir[2]});           // light.cpp:7
+    if (!(host::dot3(n, n) > 0.f)) return fail(RT_ERR_INVALID_ARGUMENT, "rt_scene_add_directional_light: zero direction");
+    rt_light_desc l{};
+    l.dir[0] = n.x; l.dir[1] = n.y; l.dir[2] = n.z;
+    for (int k = 0; k < 4; ++k) l.color[k] = host::xmcolor_roundtrip(rgba[k]);   // light.cpp:8
+    l.luminance = luminance;
+    s->lights.push_back(l);
+    return RT_OK;
+}
+int rt_scene_counts(const rt_scene* s, int32_t* ns, int32_t* nm, int32_t* nt, int32_t* nl) {
+    if (!s) return fail(RT_ERR_INVALID_ARGUMENT, "rt_scene_counts: scene is NULL");
+    if (ns) *ns = static_cast<int32_t>(s->spheres.size());
+    if (nm) *nm = static_cast<int32_t>(s->materials.size());
+    if (nt) *nt = static_cast<int32_t>(s->textures.size());
+    if (nl) *nl = static_cast<int32_t>(s->lights.size());
+    return RT_OK;
+}
+int rt_scene_export(const rt_scene* s, rt_sphere_desc* sp, rt_material_desc* ma, rt_texture_desc* te, rt_light_desc* li, float* sky_lum, int32_t* sky_tex) {
+    if (!s) return fail(RT_ERR_INVALID_ARGUMENT, "rt_scene_export: scene is NULL");
+    if (sp) std::copy(s->spheres.begin(), s->spheres.end(), sp);
+    if (ma) std::copy(s->materials.begin(), s->materials.end(), ma);
+    if (te) std::copy(s->textures.begin(), s->textures.end(), te);
+    if (li) std::copy(s->lights.begin(), s->lights.end(), li);
+    if (sky_lum) *sky_lum = s->sky_luminance;
+    if (sky_tex) *sky_tex = s->sky_texture;
+    return RT_OK;
+}
+int rt_scene_import(rt_scene* s, int32_t ns, const rt_sphere_desc* sp, int32_t nm, const rt_material_desc* ma, int32_t nt, const rt_texture_desc* te,
+                    int32_t nl, const rt_light_desc* li, float sky_lum, int32_t sky_tex) {
+    if (!s || ns < 0 || nm < 0 || nt < 0 || nl < 0 || (ns && !sp) || (nm && !ma) || (nt && !te) || (nl && !li))
+        return fail(RT_ERR_INVALID_ARGUMENT, "rt_scene_import: bad argument");
+    for (int i = 0; i < nm; ++i) {
+        if (ma[i].kind < RT_MAT_OPAQUE || ma[i].kind > RT_MAT_TRANSPARENT) return fail(RT_ERR_INVALID_ARGUMENT, "rt_scene_import: material %d has kind %d", i, ma[i].kind);
+        if (ma[i].kind != RT_MAT_TRANSPARENT && (ma[i].texture < 0 || ma[i].texture >= nt)) return fail(RT_ERR_INVALID_ARGUMENT, "rt_scene_import: material %d texture out of range", i);
+    }
+    for (int i = 0; i < ns; ++i)
+        if (sp[i].material < 0 || sp[i].material >= nm || !(sp[i].radius > 0.f)) return fail(RT_ERR_INVALID_ARGUMENT, "rt_scene_import: sphere %d invalid", i);
+    if (sky_tex < 0 || sky_tex >= nt) return fail(RT_ERR_INVALID_ARGUMENT, "rt_scene_import: sky texture out of range");
+    s->spheres.assign(sp, sp + ns); s->materials.assign(ma, ma + nm); s->textures.assign(te, te + nt); s->lights.assign(li, li + nl);
+    s->sky_luminance = sky_lum; s->sky_texture = sky_tex;
+    return RT_OK;
+}
+int rt_camera_basis_of(const rt_camera_params* cam, rt_camera_basis* out) {
+    if (!cam || !out) return fail(RT_ERR_INVALID_ARGUMENT, "rt_camera_basis_of: NULL argument");
+    host::camera_basis(*cam, *out);
+    return RT_OK;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------------
+// context
+// ------------------------------------------------------------------------------------------------
+struct EventPair { cudaEvent_t a, b; int kind; };
+
+struct rt_context {
+    int device = 0;
+    cudaStream_t stream = nullptr; bool own_stream = false;
+    cudaDeviceProp prop{};
+    int clock_khz = 0;
+    // scene
+    float4 *cullA = nullptr, *cullB = nullptr; float2* cullC = nullptr; float* radius = nullptr; rt::DevMat* mats = nullptr;
+    int n_spheres = 0, n_pad = 0;
+    bool scene_set = false, camera_set = false;
+    rt::RenderParams base{};
+    // framebuffer
+    int W = 0, H = 0;
+    float4* hdr_own = nullptr; float4* hdr_ext = nullptr;
+    uint32_t* ldr = nullptr;
+    int32_t *ids = nullptr, *mids = nullptr;
+    float4* partial = nullptr; size_t partial_bytes = 0;
+    float2 *jitter = nullptr, *lens = nullptr; size_t jitter_cap = 0, lens_cap = 0;
+    u64* counters = nullptr;   // [0] work counter, [1..4] stats
+    // settings
+    float exposure_stops = -15.f; uint32_t seed = 0; int chunk_spp = 0;
+    // instrumentation
+    std::vector<EventPair> pending; std::vector<EventPair> pool;
+    double render_ms = 0, resolve_ms = 0; int launches = 0;
+    u64 stat_base[4] = {0, 0, 0, 0};
+    int render_blocks_per_sm = 0;
+
+    float4* hdr() const { return hdr_ext ? hdr_ext : hdr_own; }
+};
+
+static int ctx_use(rt_context* c) {
+    RT_CUDA(cudaSetDevice(c->device));
+    return RT_OK;
+}
+static EventPair ev_begin(rt_context* c, int kind) {
+    EventPair e;
+    if (!c->pool.empty()) { e = c->pool.back(); c->pool.pop_back(); }
+    else { cudaEventCreate(&e.a); cudaEventCreate(&e.b); }
+    e.kind = kind;
+    cudaEventRecord(e.a, c->stream);
+    return e;
+}
+static void ev_end(rt_context* c, EventPair e) { cudaEventRecord(e.b, c->stream); c->pending.push_back(e); }
+static void ev_collect(rt_context* c) {
+    for (auto& e : c->pending) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, e.a, e.b) == cudaSuccess) { if (e.kind == 0) c->render_ms += ms; else c->resolve_ms += ms; }
+        c->pool.push_back(e);
+    }
+    c->pending.clear();
+}
+template <class T> static int dev_realloc(T*& p, size_t n) {
+    if (p) { cudaFree(p); p = nullptr; }
+    if (n == 0) return RT_OK;
+    RT_CUDA(cudaMalloc(&p, n * sizeof(T)));
+    return RT_OK;
+}
+static size_t scene_smem_bytes(int n_pad) { return static_cast<size_t>(n_pad / 2) * 40u + static_cast<size_t>(n_pad) * 4u; }
+
+extern "C" {
+
+int rt_context_create(int device, rt_context** out) {
+    if (!out) return fail(RT_ERR_INVALID_ARGUMENT, "rt_context_create: out is NULL");
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0)
+        return fail(RT_ERR_CUDA, "rt_context_create: no CUDA device available (%s); this library has no CPU fallback", cudaGetErrorString(e));
+    if (device < 0 || device >= n) return fail(RT_ERR_INVALID_ARGUMENT, "rt_context_create: device %d out of range [0,%d)", device, n);
+    RT_CUDA(cudaSetDevice(device));
+    rt_context* c = new rt_context();
+    c->device = device;
+    if (cudaGetDeviceProperties(&c->prop, device) != cudaSuccess) { delete c; return fail(RT_ERR_CUDA, "cudaGetDeviceProperties failed"); }
+    if (c->prop.major < 10) {
+        const int maj = c->prop.major, min = c->prop.minor; delete c;
+        return fail(RT_ERR_UNSUPPORTED, "rt_context_create: device is sm_%d%d; this build contains sm_100a code only", maj, min);
+    }
+    cudaDeviceGetAttribute(&c->clock_khz, cudaDevAttrClockRate, device);
+    if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return fail(RT_ERR_CUDA, "cudaStreamCreate failed"); }
+    c->own_stream = true;
+    if (cudaMalloc(&c->counters, 8 * sizeof(u64)) != cudaSuccess) { delete c; return fail(RT_ERR_OUT_OF_MEMORY, "cudaMalloc(counters) failed"); }
+    cudaMemset(c->counters, 0, 8 * sizeof(u64));
+    *out = c;
+    return RT_OK;
+}
+void rt_context_destroy(rt_context* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    ev_collect(c);
+    for (auto& e : c->pool) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
+    cudaFree(c->cullA); cudaFree(c->cullB); cudaFree(c->cullC); cudaFree(c->radius); cudaFree(c->mats);
+    cudaFree(c->hdr_own); cudaFree(c->ldr); cudaFree(c->ids); cudaFree(c->mids); cudaFree(c->partial);
+    cudaFree(c->jitter); cudaFree(c->lens); cudaFree(c->counters);
+    if (c->own_stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+int rt_set_stream(rt_context* c, void* s) {
+    if (!c) return fail(RT_ERR_INVALID_ARGUMENT, "rt_set_stream: ctx is NULL");
+    if (int r = ctx_use(c)) return r;
+    RT_CUDA(cudaStreamSynchronize(c->stream));
+    if (c->own_stream) { cudaStreamDestroy(c->stream); c->own_stream = false; }
+    c->stream = static_cast<cudaStream_t>(s);
+    return RT_OK;
+}
+int rt_synchronize(rt_context* c) {
+    if (!c) return fail(RT_ERR_INVALID_ARGUMENT, "rt_synchronize: ctx is NULL");
+    if (int r = ctx_use(c)) return r;
+    RT_CUDA(cudaStreamSynchronize(c->stream));
+    return RT_OK;
+}
+int rt_set_exposure(rt_context* c, float stops) { if (!c) return fail(RT_ERR_INVALID_ARGUMENT, "rt_set_exposure: ctx is NULL"); c->exposure_stops = stops; return RT_OK; }
+int rt_set_seed(rt_context* c, uint32_t seed) { if (!c) return fail(RT_ERR_INVALID_ARGUMENT, "rt_set_seed: ctx is NULL"); c->seed = seed; return RT_OK; }
+int rt_set_chunk_spp(rt_context* c, int chunk) {
+    if (!c || chunk < 0) return fail(RT_ERR_INVALID_ARGUMENT, "rt_set_chunk_spp: bad argument");
+    c->chunk_spp = chunk; return RT_OK;
+}
+
+int rt_set_scene(rt_context* c, const rt_scene* s) {
+    if (!c || !s) return fail(RT_ERR_INVALID_ARGUMENT, "rt_set_scene: NULL argument");
+    if (s->sky_texture < 0) return fail(RT_ERR_NOT_READY, "rt_set_scene: the scene has no sky (rt_scene_set_sky)");
+    if (s->lights.size() > 1) return fail(RT_ERR_UNSUPPORTED, "rt_set_scene: %zu lights given; this build fuses exactly one shadow query per vertex (0 or 1 directional light)", s->lights.size());
+    if (int r = ctx_use(c)) return r;
+    const int n = static_cast<int>(s->spheres.size());
+    const int n_pad = std::max(32, (n + 31) / 32 * 32);
+    const int np = n_pad / 2;
+    if (scene_smem_bytes(n_pad) > static_cast<size_t>(c->prop.sharedMemPerBlockOptin))
+        return fail(RT_ERR_UNSUPPORTED, "rt_set_scene: %d spheres need %zu B of shared memory per CTA, device limit is %zu", n, scene_smem_bytes(n_pad), static_cast<size_t>(c->prop.sharedMemPerBlockOptin));
+    const bool has_light = !s->lights.empty();
+    double L[3] = {0, 0, 0};
+    if (has_light) for (int k = 0; k < 3; ++k) L[k] = s->lights[0].dir[k];
+    std::vector<float4> A(np), B(np); std::vector<float2> C(np); std::vector<float> R(n_pad, 0.f);
+    std::vector<rt::DevMat> M(std::max(n, 1));
+    const double K = static_cast<double>(RT_CULL_K);
+    auto sphere_terms = [&](int i, float& cx, float& cy, float& cz, float& wn, float& ncl) {
+        if (i >= n) { cx = cy = cz = 0.f; wn = RT_PAD_W; ncl = 0.f; return; }
+        const rt_sphere_desc& sp = s->spheres[i];
+        cx = sp.cx; cy = sp.cy; cz = sp.cz;
+        const double cc = static_cast<double>(sp.cx) * sp.cx + static_cast<double>(sp.cy) * sp.cy + static_cast<double>(sp.cz) * sp.cz;
+        const double r2 = static_cast<double>(sp.radius) * sp.radius;
+        wn = static_cast<float>(r2 - cc + K * (cc + r2));            // -(|c|^2 - r^2) + slack
+        ncl = static_cast<float>(-(sp.cx * L[0] + sp.cy * L[1] + sp.cz * L[2]));
+        R[i] = sp.radius;
+    };
+    for (int p = 0; p < np; ++p) {
+        float cx0, cy0, cz0, w0, l0, cx1, cy1, cz1, w1, l1;
+        sphere_terms(2 * p, cx0, cy0, cz0, w0, l0);
+        sphere_terms(2 * p + 1, cx1, cy1, cz1, w1, l1);
+        A[p] = make_float4(cx0, cx1, cy0, cy1);
+        B[p] = make_float4(cz0, cz1, w0, w1);
+        C[p] = make_float2(l0, l1);
+    }
+    for (int i = 0; i < n; ++i) {
+        const rt_material_desc& m = s->materials[s->spheres[i].material];
+        rt::DevMat dm{}; dm.kind = m.kind; dm.smoothness = m.smoothness; dm.ior = m.ior;
+        if (m.texture >= 0) {
+            const rt_texture_desc& t = s->textures[m.texture];
+            dm.tex_kind = t.kind; dm.tiling = t.tiling;
+            for (int k = 0; k < 4; ++k) { dm.c0[k] = t.c0[k]; dm.c1[k] = t.c1[k]; }
+        }
+        M[i] = dm;
+    }
+    if (int r = dev_realloc(c->cullA, np)) return r;
+    if (int r = dev_realloc(c->cullB, np)) return r;
+    if (int r = dev_realloc(c->cullC, np)) return r;
+    if (int r = dev_realloc(c->radius, n_pad)) return r;
+    if (int r = dev_realloc(c->mats, M.size())) return r;
+    RT_CUDA(cudaMemcpyAsync(c->cullA, A.data(), np * sizeof(float4), cudaMemcpyHostToDevice, c->stream));
+    RT_CUDA(cudaMemcpyAsync(c->cullB, B.data(), np * sizeof(float4), cudaMemcpyHostToDevice, c->stream));
+    RT_CUDA(cudaMemcpyAsync(c->cullC, C.data(), np * sizeof(float2), cudaMemcpyHostToDevice, c->stream));
+    RT_CUDA(cudaMemcpyAsync(c->radius, R.data(), n_pad * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+    RT_CUDA(cudaMemcpyAsync(c->mats, M.data(), M.size() * sizeof(rt::DevMat), cudaMemcpyHostToDevice, c->stream));
+    RT_CUDA(cudaStreamSynchronize(c->stream));
+    rt::RenderParams& b = c->base;
+    b.cullA = c->cullA; b.cullB = c->cullB; b.cullC = c->cullC; b.radius = c->radius; b.mats = c->mats;
+    b.n_spheres = n; b.n_pairs_pad = np; b.n_groups = n_pad / 32; b.n_lights = has_light ? 1 : 0;
+    b.Lx = b.Ly = b.Lz = 0.f; b.lcx = b.lcy = b.lcz = 0.f;
+    if (has_light) {
+        const rt_light_desc& l = s->lights[0];
+        b.Lx = l.dir[0]; b.Ly = l.dir[1]; b.Lz = l.dir[2];
+        b.lcx = l.luminance * l.color[0]; b.lcy = l.luminance * l.color[1]; b.lcz = l.luminance * l.color[2];   // light.cpp:27
+    }
+    const rt_texture_desc& sky = s->textures[s->sky_texture];              // Emissive::Emit at uv = (0,0): material.cpp:172-175
+    const float* sc = sky.c0;                                             // checker at (0,0): u%2 == v%2 -> colour 0
+    b.skyx = s->sky_luminance * sc[0]; b.skyy = s->sky_luminance * sc[1]; b.skyz = s->sky_luminance * sc[2];
+    c->n_spheres = n; c->n_pad = n_pad; c->scene_set = true;
+    // opt in to large dynamic shared memory and size the persistent grid
+    const size_t smem = scene_smem_bytes(n_pad);
+    RT_CUDA(cudaFuncSetAttribute(rt::rt_render_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    RT_CUDA(cudaFuncSetAttribute(rt::rt_render_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    RT_CUDA(cudaFuncSetAttribute(rt::rt_primary_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    RT_CUDA(cudaFuncSetAttribute(rt::rt_primary_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    int bps = 0;
+    RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, rt::rt_render_kernel<false>, 256, smem));
+    if (bps < 1) return fail(RT_ERR_UNSUPPORTED, "rt_set_scene: render kernel does not fit on an SM with %zu B shared memory", smem);
+    c->render_blocks_per_sm = bps;
+    return RT_OK;
+}
+
+int rt_set_camera(rt_context* c, const rt_camera_params* cam) {
+    if (!c || !cam) return fail(RT_ERR_INVALID_ARGUMENT, "rt_set_camera: NULL argument");
+    if (!finite3(cam->origin) || !finite3(cam->look_at) || !(cam->vfov_deg > 0.f && cam->vfov_deg < 180.f) || !(cam->aspect > 0.f))
+        return fail(RT_ERR_INVALID_ARGUMENT, "rt_set_camera: non-finite position or fov/aspect out of range");
+    rt_camera_basis b; host::camera_basis(*cam, b);
+    rt::DevCamera& d = c->base.cam;
+    d.ox = b.origin[0]; d.oy = b.origin[1]; d.oz = b.origin[2];
+    d.xx = b.x[0]; d.xy = b.x[1]; d.xz = b.x[2];
+    d.yx = b.y[0]; d.yy = b.y[1]; d.yz = b.y[2];
+    d.ix = b.image_origin[0]; d.iy = b.image_origin[1]; d.iz = b.image_origin[2];
+    d.aperture = b.aperture; d.focus = b.focus;
+    c->camera_set = true;
+    return RT_OK;
+}
+
+int rt_framebuffer_resize(rt_context* c, int W, int H) {
+    if (!c || W <= 0 || H <= 0 || static_cast<int64_t>(W) * H > (1ll << 30)) return fail(RT_ERR_INVALID_ARGUMENT, "rt_framebuffer_resize: bad size %dx%d", W, H);
+    if (int r = ctx_use(c)) return r;
+    RT_CUDA(cudaStreamSynchronize(c->stream));
+    const size_t n = static_cast<size_t>(W) * H;
+    if (int r = dev_realloc(c->hdr_own, n)) return r;
+    if (int r = dev_realloc(c->ldr, n)) return r;
+    if (int r = dev_realloc(c->ids, n)) return r;
+    if (int r = dev_realloc(c->mids, n)) return r;
+    c->hdr_ext = nullptr;
+    c->W = W; c->H = H;
+    return rt_framebuffer_clear(c);
+}
+int rt_framebuffer_clear(rt_context* c) {
+    if (!c || !c->hdr()) return fail(RT_ERR_NOT_READY, "rt_framebuffer_clear: no framebuffer");
+    if (int r = ctx_use(c)) return r;
+    const size_t n = static_cast<size_t>(c->W) * c->H;
+    RT_CUDA(cudaMemsetAsync(c->hdr(), 0, n * sizeof(float4), c->stream));     // InitBuffers, app.cpp:112-119
+    RT_CUDA(cudaMemsetAsync(c->ldr, 0, n * sizeof(uint32_t), c->stream));
+    return RT_OK;
+}
+void* rt_hdr_device_ptr(rt_context* c) { return c ? c->hdr() : nullptr; }
+int rt_hdr_bind_external(rt_context* c, void* p) {
+    if (!c) return fail(RT_ERR_INVALID_ARGUMENT, "rt_hdr_bind_external: ctx is NULL");
+    if (!c->hdr_own) return fail(RT_ERR_NOT_READY, "rt_hdr_bind_external: call rt_framebuffer_resize first");
+    if (p && (reinterpret_cast<uintptr_t>(p) & 15u)) return fail(RT_ERR_INVALID_ARGUMENT, "rt_hdr_bind_external: pointer must be 16-byte aligned");
+    c->hdr_ext = static_cast<float4*>(p);
+    return RT_OK;
+}
+
+// Fills RenderParams for a launch and uploads the per-frame Halton tables.
+static int prepare_frames(rt_context* c, u64 first_sample, int spp, int max_depth, uint32_t flags, rt::RenderParams& p) {
+    p = c->base;
+    p.W = c->W; p.H = c->H; p.tiles_x = (c->W + 7) / 8; p.tiles_y = (c->H + 3) / 4;
+    p.first_sample = first_sample; p.spp = spp; p.max_depth = max_depth; p.flags = flags; p.seed = c->seed;
+    p.exposure = static_cast<float>(std::pow(2, c->exposure_stops));          // spheres-app.cpp:174
+    p.hdr = c->hdr(); p.work_counter = c->counters; p.stats = c->counters + 1;
+    // frame jitter Halton2D(n; 2,3) and lens samples HaltonSampleDisk(n+i+j; 4,5), spheres-app.cpp:140,152
+    const size_t n_lens = static_cast<size_t>(spp) + c->W + c->H;
+    if (c->jitter_cap < static_cast<size_t>(spp)) { if (int r = dev_realloc(c->jitter, spp)) return r; c->jitter_cap = spp; }
+    if (c->lens_cap < n_lens) { if (int r = dev_realloc(c->lens, n_lens)) return r; c->lens_cap = n_lens; }
+    std::vector<float2> hj(spp), hl(n_lens);
+    for (int s = 0; s < spp; ++s) { const u64 n = first_sample + s; hj[s] = make_float2(host::halton(n, 2), host::halton(n, 3)); }
+    for (size_t k = 0; k < n_lens; ++k) {
+        const u64 idx = first_sample + k;
+        const float theta = RT_TWO_PI * host::halton(idx, 4);                 // quasi-random.cpp:54
+        const float r = host::halton(idx, 5);                                 // :55
+        float sn, cs; rt::sincos_pinned(theta, &sn, &cs);
+        hl[k] = make_float2(r * cs, r * sn);                                  // :57-60
+    }
+    RT_CUDA(cudaMemcpyAsync(c->jitter, hj.data(), spp * sizeof(float2), cudaMemcpyHostToDevice, c->stream));
+    RT_CUDA(cudaMemcpyAsync(c->lens, hl.data(), n_lens * sizeof(float2), cudaMemcpyHostToDevice, c->stream));
+    RT_CUDA(cudaStreamSynchronize(c->stream));   // hj/hl are stack-owned pageable buffers
+    p.jitter = c->jitter; p.lens = c->lens;
+    return RT_OK;
+}
+
+int rt_render(rt_context* c, uint64_t first_sample, int spp, int max_depth, uint32_t flags) {
+    if (!c) return fail(RT_ERR_INVALID_ARGUMENT, "rt_render: ctx is NULL");
+    if (!c->scene_set || !c->camera_set || !c->hdr()) return fail(RT_ERR_NOT_READY, "rt_render: scene, camera and framebuffer must be set first");
+    if (first_sample < 1 || spp < 0 || max_depth < 0) return fail(RT_ERR_INVALID_ARGUMENT, "rt_render: first_sample >= 1, spp >= 0, max_depth >= 0 required");
+    if (flags & ~(RT_FLAG_JITTER_OFF | RT_FLAG_LENS_OFF | RT_FLAG_DEBUG_NO_CULL_)) return fail(RT_ERR_INVALID_ARGUMENT, "rt_render: unknown flag bits 0x%x", flags);
+    if (spp == 0) return RT_OK;
+    if (int r = ctx_use(c)) return r;
+    rt::RenderParams p;
+    if (int r = prepare_frames(c, first_sample, spp, max_depth, flags, p)) return r;
+    // work items: (chunk of samples) x (pixel).  One chunk keeps the reference's sequential per-pixel sum order.
+    int chunk = c->chunk_spp;
+    if (chunk <= 0) { const int n_chunks = spp <= 16 ? 1 : std::min(16, spp / 8); chunk = (spp + n_chunks - 1) / n_chunks; }
+    chunk = std::min(chunk, spp);
+    p.chunk_spp = chunk; p.n_chunks = (spp + chunk - 1) / chunk;
+    const size_t n_pix = static_cast<size_t>(c->W) * c->H;
+    p.partial = nullptr;
+    if (p.n_chunks > 1) {
+        const size_t need = n_pix * p.n_chunks * sizeof(float4);
+        if (c->partial_bytes < need) {
+            if (c->partial) { cudaFree(c->partial); c->partial = nullptr; c->partial_bytes = 0; }
+            RT_CUDA(cudaMalloc(&c->partial, need)); c->partial_bytes = need;
+        }
+        p.partial = c->partial;
+    }
+    RT_CUDA(cudaMemsetAsync(c->counters, 0, sizeof(u64), c->stream));
+    const size_t smem = scene_smem_bytes(c->n_pad);
+    const int grid = c->prop.multiProcessorCount * c->render_blocks_per_sm;
+    EventPair ev = ev_begin(c, 0);
+    if (flags & RT_FLAG_DEBUG_NO_CULL_) rt::rt_render_kernel<true><<<grid, 256, smem, c->stream>>>(p);
+    else rt::rt_render_kernel<false><<<grid, 256, smem, c->stream>>>(p);
+    ++c->launches;
+    if (p.n_chunks > 1) {
+        rt::rt_combine_kernel<<<static_cast<unsigned>((n_pix + 255) / 256), 256, 0, c->stream>>>(p.hdr, p.partial, p.n_chunks, n_pix);
+        ++c->launches;
+    }
+    ev_end(c, ev);
+    RT_CUDA(cudaGetLastError());
+    return RT_OK;
+}
+
+int rt_read_hdr_sum(rt_context* c, float* rgba, size_t n_pixels) {
+    if (!c || !rgba) return fail(RT_ERR_INVALID_ARGUMENT, "rt_read_hdr_sum: NULL argument");
+    if (!c->hdr()) return fail(RT_ERR_NOT_READY, "rt_read_hdr_sum: no framebuffer");
+    if (n_pixels != static_cast<size_t>(c->W) * c->H) return fail(RT_ERR_INVALID_ARGUMENT, "rt_read_hdr_sum: n_pixels %zu != %d*%d", n_pixels, c->W, c->H);
+    if (int r = ctx_use(c)) return r;
+    RT_CUDA(cudaMemcpyAsync(rgba, c->hdr(), n_pixels * sizeof(float4), cudaMemcpyDeviceToHost, c->stream));
+    RT_CUDA(cudaStreamSynchronize(c->stream));
+    return RT_OK;
+}
+int rt_write_hdr_sum(rt_context* c, const float* rgba, size_t n_pixels) {
+    if (!c || !rgba) return fail(RT_ERR_INVALID_ARGUMENT, "rt_write_hdr_sum: NULL argument");
+    if (!c->hdr()) return fail(RT_ERR_NOT_READY, "rt_write_hdr_sum: no framebuffer");
+    if (n_pixels != static_cast<size_t>(c->W) * c->H) return fail(RT_ERR_INVALID_ARGUMENT, "rt_write_hdr_sum: n_pixels mismatch");
+    if (int r = ctx_use(c)) return r;
+    RT_CUDA(cudaMemcpyAsync(c->hdr(), rgba, n_pixels * sizeof(float4), cudaMemcpyHostToDevice, c->stream));
+    RT_CUDA(cudaStreamSynchronize(c->stream));
+    return RT_OK;
+}
+int rt_resolve_ldr(rt_context* c, uint64_t sample_count, uint32_t* bgra8, size_t n_pixels) {
+    if (!c) return fail(RT_ERR_INVALID_ARGUMENT, "rt_resolve_ldr: ctx is NULL");
+    if (!c->hdr()) return fail(RT_ERR_NOT_READY, "rt_resolve_ldr: no framebuffer");
+    if (sample_count < 1) return fail(RT_ERR_INVALID_ARGUMENT, "rt_resolve_ldr: sample_count must be >= 1");
+    const size_t n = static_cast<size_t>(c->W) * c->H;
+    if (bgra8 && n_pixels != n) return fail(RT_ERR_INVALID_ARGUMENT, "rt_resolve_ldr: n_pixels mismatch");
+    if (int r = ctx_use(c)) return r;
+    const int grid = c->prop.multiProcessorCount * 8;
+    EventPair ev = ev_begin(c, 1);
+    rt::rt_resolve_kernel<<<grid, 256, 0, c->stream>>>(c->hdr(), c->ldr, static_cast<float>(sample_count), n);
+    ev_end(c, ev);
+    ++c->launches;
+    RT_CUDA(cudaGetLastError());
+    if (bgra8) {
+        RT_CUDA(cudaMemcpyAsync(bgra8, c->ldr, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+        RT_CUDA(cudaStreamSynchronize(c->stream));
+    }
+    return RT_OK;
+}
+int rt_primary_hits(rt_context* c, uint64_t sample, uint32_t flags, int32_t* sphere_idx, int32_t* material_id, size_t n_pixels) {
+    if (!c) return fail(RT_ERR_INVALID_ARGUMENT, "rt_primary_hits: ctx is NULL");
+    if (!c->scene_set || !c->camera_set || !c->hdr()) return fail(RT_ERR_NOT_READY, "rt_primary_hits: scene, camera and framebuffer must be set first");
+    const size_t n = static_cast<size_t>(c->W) * c->H;
+    if (n_pixels != n || sample < 1) return fail(RT_ERR_INVALID_ARGUMENT, "rt_primary_hits: n_pixels mismatch or sample < 1");
+    if (int r = ctx_use(c)) return r;
+    rt::RenderParams p;
+    if (int r = prepare_frames(c, sample, 1, 0, flags, p)) return r;
+    p.chunk_spp = 1; p.n_chunks = 1;
+    const size_t smem = scene_smem_bytes(c->n_pad);
+    const int grid = c->prop.multiProcessorCount * std::max(1, c->render_blocks_per_sm);
+    if (flags & RT_FLAG_DEBUG_NO_CULL_) rt::rt_primary_kernel<true><<<grid, 256, smem, c->stream>>>(p, c->ids, c->mids);
+    else rt::rt_primary_kernel<false><<<grid, 256, smem, c->stream>>>(p, c->ids, c->mids);
+    ++c->launches;
+    RT_CUDA(cudaGetLastError());
+    if (sphere_idx) RT_CUDA(cudaMemcpyAsync(sphere_idx, c->ids, n * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+    if (material_id) RT_CUDA(cudaMemcpyAsync(material_id, c->mids, n * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+    RT_CUDA(cudaStreamSynchronize(c->stream));
+    return RT_OK;
+}
+int rt_get_stats(rt_context* c, rt_stats* out) {
+    if (!c || !out) return fail(RT_ERR_INVALID_ARGUMENT, "rt_get_stats: NULL argument");
+    if (int r = ctx_use(c)) return r;
+    RT_CUDA(cudaStreamSynchronize(c->stream));
+    ev_collect(c);
+    u64 h[5] = {0, 0, 0, 0, 0};
+    RT_CUDA(cudaMemcpy(h, c->counters, 5 * sizeof(u64), cudaMemcpyDeviceToHost));
+    memset(out, 0, sizeof *out);
+    out->closest_rays = h[1] - c->stat_base[0]; out->shadow_rays = h[2] - c->stat_base[1];
+    out->passes = h[3] - c->stat_base[2]; out->paths = h[4] - c->stat_base[3];
+    out->sphere_tests = static_cast<u64>(c->n_spheres) * (out->closest_rays + out->shadow_rays);
+    out->render_ms = c->render_ms; out->resolve_ms = c->resolve_ms;
+    out->sm_count = c->prop.multiProcessorCount; out->clock_khz = c->clock_khz; out->launches = c->launches;
+    return RT_OK;
+}
+int rt_stats_reset(rt_context* c) {
+    if (!c) return fail(RT_ERR_INVALID_ARGUMENT, "rt_stats_reset: ctx is NULL");
+    if (int r = ctx_use(c)) return r;
+    RT_CUDA(cudaStreamSynchronize(c->stream));
+    ev_collect(c);
+    u64 h[5];
+    RT_CUDA(cudaMemcpy(h, c->counters, 5 * sizeof(u64), cudaMemcpyDeviceToHost));
+    for (int k = 0; k < 4; ++k) c->stat_base[k] = h[k + 1];
+    c->render_ms = c->resolve_ms = 0; c->launches = 0;
+    return RT_OK;
+}
+
+}  // extern "C"

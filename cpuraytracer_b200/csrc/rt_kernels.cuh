@@ -1,0 +1,307 @@
+// rt_kernels.cuh -- the sm_100a kernels of the `src/spheres` hot path.
+//   rt_render_kernel   K1-K4 fused persistent megakernel: ray generation (spheres-app.cpp:132-161 +
+//                      camera.cpp:30-48), closest hit + shadow query (ray-tracing.cpp:42-84,
+//                      light.cpp:13-18), scatter (material.cpp:20-164), direct light (light.cpp:11-42),
+//                      integrator (spheres-app.cpp:238-257) and per-pixel accumulation (:177-184).
+//   rt_combine_kernel  adds the per-chunk partial sums to the running sum in a fixed order.
+//   rt_resolve_kernel  K5: mean, ACES, gamma, BGRA8 (spheres-app.cpp:186-214).
+//   rt_primary_kernel  K6: primary-hit sphere / material id buffers.
+#pragma once
+#include "rt_device.cuh"
+
+namespace rt {
+
+struct RenderParams {
+    // scene (global memory; the cull arrays are staged into shared memory by every CTA)
+    const float4* cullA; const float4* cullB; const float2* cullC; const float* radius;
+    const DevMat* mats;
+    int n_spheres, n_pairs_pad, n_groups;
+    int n_lights;
+    float Lx, Ly, Lz;            // normalised light direction (light.cpp:7)
+    float lcx, lcy, lcz;         // luminance * colour
+    float skyx, skyy, skyz;      // sky luminance * colour (material.cpp:172-175)
+    DevCamera cam;
+    // frame
+    int W, H, tiles_x, tiles_y;
+    u64 first_sample;            // m_sampleCount of the first frame
+    int spp, chunk_spp, n_chunks, max_depth;
+    uint32_t flags, seed;
+    float exposure;              // 2^m_exposure (spheres-app.cpp:174)
+    const float2* jitter;        // [spp]  Halton(2,3) frame jitter (spheres-app.cpp:140)
+    const float2* lens;          // [spp + W + H - 1]  HaltonSampleDisk(n+i+j; 4,5) (spheres-app.cpp:152)
+    float4* hdr;                 // running sum, m_backbufferHdr
+    float4* partial;             // [n_chunks][W*H] when n_chunks > 1
+    u64* work_counter;
+    u64* stats;                  // [0] closest rays [1] shadow rays [2] warp passes [3] paths
+};
+
+#define RT_FLAG_JITTER_OFF_ 1u
+#define RT_FLAG_LENS_OFF_ 2u
+#define RT_FLAG_DEBUG_NO_CULL_ 0x100u
+
+enum LaneState { ST_NEED_ITEM = 0, ST_NEW_PATH = 1, ST_IN_PATH = 2, ST_DONE = 3 };
+
+__device__ __forceinline__ void stage_scene(const RenderParams& p, float4*& sA, float4*& sB, float2*& sC, float*& sR, unsigned char* smem) {
+    const int np = p.n_pairs_pad;
+    sA = reinterpret_cast<float4*>(smem);
+    sB = sA + np;
+    sC = reinterpret_cast<float2*>(sB + np);
+    sR = reinterpret_cast<float*>(sC + np);
+    for (int i = threadIdx.x; i < np; i += blockDim.x) { sA[i] = p.cullA[i]; sB[i] = p.cullB[i]; sC[i] = p.cullC[i]; }
+    for (int i = threadIdx.x; i < 2 * np; i += blockDim.x) sR[i] = p.radius[i];
+    __syncthreads();
+}
+
+// Unshadowed DirectionalLight::Shade (light.cpp:20-40) for one light; the occlusion test is resolved by the
+// next fused pass (the shadow ray shares its origin with the scattered ray).
+__device__ __forceinline__ V3 direct_unshadowed(const RenderParams& p, const DevMat& m, V3 pos, V3 n, float u, float v) {
+    V3 albedo = mk3(0.f, 0.f, 0.f), f0 = mk3(0.04f, 0.04f, 0.04f);            // material.h:27-29,43-45,60-62
+    if (m.kind == 0) albedo = texture_rgb(m, u, v);
+    else if (m.kind == 1) f0 = texture_rgb(m, u, v);
+    const float s = m.smoothness;
+    const V3 L = mk3(p.Lx, p.Ly, p.Lz);
+    const float n_dot_l = saturate1(dot3(n, L));                               // light.cpp:26
+    const V3 rin = mk3(p.lcx * n_dot_l, p.lcy * n_dot_l, p.lcz * n_dot_l);     // :27
+    const V3 view = normalize3(mk3(p.cam.ox, p.cam.oy, p.cam.oz) - pos);       // :33 (camera origin, spheres-app.cpp:250)
+    const V3 half = normalize3(L + view);                                      // :34
+    const float n_dot_h = saturate1(dot3(n, half));                            // :35
+    const float n_dot_v = saturate1(dot3(view, n));                            // :36
+    const float pw5 = pow5(1.0f - n_dot_v);
+    const float pw = powf(n_dot_h, s);                                         // :38
+    const float k = s + 8.f;
+    const V3 refl = mk3(f0.x + (1.0f - f0.x) * pw5, f0.y + (1.0f - f0.y) * pw5, f0.z + (1.0f - f0.z) * pw5);   // :37
+    const V3 spec = mk3(((refl.x * 0.125f) * k) * pw, ((refl.y * 0.125f) * k) * pw, ((refl.z * 0.125f) * k) * pw);
+    return rin * (albedo + spec);                                              // :40
+}
+
+// Material::Scatter, material.cpp:20-164.  Returns false when the path ends here.
+__device__ __forceinline__ bool scatter(const DevMat& m, V3 d, V3 pos, V3 n, float u, float v,
+                                        float xi, float u1, float u2, V3& atten, V3& out_d) {
+    if (m.kind == 0) {                                                         // DielectricOpaque
+        const float ndv = dot3(neg3(d), n);
+        if (!(ndv > 0.f)) return false;                                        // :22
+        const float refl = schlick(0.04f, saturate1(ndv));                     // :25-27
+        if (refl > xi) {                                                       // :29-30
+            atten = mk3(1.f, 1.f, 1.f);
+            out_d = normalize3(reflect3(d, n));                                // :35
+            return true;
+        }
+        atten = texture_rgb(m, u, v);                                          // :41
+        const V3 dir = hemisphere_from_u(u1, u2);                              // :44
+        const V3 up = fabsf(n.x) < 0.5f ? mk3(1.f, 0.f, 0.f) : mk3(0.f, 1.f, 0.f);   // :50
+        const V3 b1 = cross3(up, n);                                           // :51
+        const V3 b2 = cross3(n, b1);                                           // :52
+        out_d = normalize3((dir.x * b1 + dir.y * b2) + dir.z * n);             // :55-56
+        return true;
+    }
+    if (m.kind == 1) {                                                         // Metal: always reflects (alpha lane, :81-85)
+        const float ndv = dot3(neg3(d), n);
+        if (!(ndv > 0.f)) return false;                                        // :74
+        atten = texture_rgb(m, u, v);                                          // :87
+        out_d = normalize3(reflect3(d, n));                                    // :89
+        return true;
+    }
+    atten = mk3(1.f, 1.f, 1.f);                                                // DielectricTransparent :114
+    V3 outward; float eta, cos_i;
+    const float dn = dot3(d, n);
+    if (dn > 0.f) { outward = neg3(n); eta = m.ior; cos_i = dn; }              // :121-127
+    else { outward = n; eta = 1.0f / m.ior; cos_i = dot3(d, neg3(n)); }        // :128-134 (exact reciprocal)
+    const V3 refr = refract3(d, outward, eta);                                 // :137
+    const bool can_refract = (refr.x != 0.f) || (refr.y != 0.f) || (refr.z != 0.f);
+    const float prob = can_refract ? fresnel_term(cos_i, m.ior) : 1.0f;        // :140-149
+    out_d = (prob > xi) ? normalize3(reflect3(d, n)) : normalize3(refr);       // :153-161
+    return true;
+}
+
+// Maps a linear work index to (chunk, pixel).  Pixels are enumerated in 8x4 tiles so the 32 lanes of a warp
+// start on a compact screen tile (coherent primary rays); chunks are the outer loop.
+__device__ __forceinline__ bool item_to_pixel(const RenderParams& p, u64 item, int& chunk, int& px, int& py) {
+    const u64 per_chunk = static_cast<u64>(p.tiles_x) * p.tiles_y * 32ull;
+    chunk = static_cast<int>(item / per_chunk);
+    const uint32_t r = static_cast<uint32_t>(item % per_chunk);
+    const uint32_t tile = r >> 5, in = r & 31u;
+    px = static_cast<int>((tile % p.tiles_x) * 8u + (in & 7u));
+    py = static_cast<int>((tile / p.tiles_x) * 4u + (in >> 3));
+    return px < p.W && py < p.H;
+}
+
+template <bool NO_CULL>
+__global__ void __launch_bounds__(256) rt_render_kernel(const RenderParams p) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    float4 *sA, *sB; float2* sC; float* sR;
+    stage_scene(p, sA, sB, sC, sR, smem);
+
+    const unsigned FULL = 0xffffffffu;
+    const unsigned lane = threadIdx.x & 31u;
+    const u64 n_items = static_cast<u64>(p.tiles_x) * p.tiles_y * 32ull * static_cast<u64>(p.n_chunks);
+    const V3 Ldir = mk3(p.Lx, p.Ly, p.Lz);
+    const V3 sky = mk3(p.skyx, p.skyy, p.skyz);
+    const bool has_light = p.n_lights > 0;
+
+    int st = ST_NEED_ITEM;
+    int pix = 0, px = 0, py = 0, chunk = 0, s_cur = 0, s_end = 0, depth = 0;
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    V3 o = mk3(0.f, 0.f, 0.f), d = mk3(0.f, 0.f, 1.f);
+    V3 T = mk3(1.f, 1.f, 1.f), Lsum = mk3(0.f, 0.f, 0.f), pend = mk3(0.f, 0.f, 0.f);
+    bool want_closest = false, want_shadow = false;
+    uint32_t n_closest = 0, n_shadow = 0, n_pass = 0, n_paths = 0;
+
+    for (;;) {
+        // ---- work distribution: warp-aggregated fetch from the global queue ----
+        const unsigned need = __ballot_sync(FULL, st == ST_NEED_ITEM);
+        if (need) {
+            const int leader = __ffs(need) - 1;
+            u64 base = 0;
+            if (static_cast<int>(lane) == leader) base = atomicAdd(p.work_counter, static_cast<u64>(__popc(need)));
+            base = __shfl_sync(FULL, base, leader);
+            if (st == ST_NEED_ITEM) {
+                const u64 item = base + __popc(need & ((1u << lane) - 1u));
+                if (item >= n_items) st = ST_DONE;
+                else if (item_to_pixel(p, item, chunk, px, py)) {
+                    pix = py * p.W + px;
+                    s_cur = chunk * p.chunk_spp;
+                    s_end = min(p.spp, s_cur + p.chunk_spp);
+                    acc = (p.n_chunks == 1) ? p.hdr[pix] : make_float4(0.f, 0.f, 0.f, 0.f);
+                    st = ST_NEW_PATH;
+                }
+            }
+        }
+        if (__all_sync(FULL, st == ST_DONE)) break;
+
+        // ---- K1: primary ray (GenerateRays + Camera::GetRay) ----
+        if (st == ST_NEW_PATH) {
+            float jx = 0.f, jy = 0.f, lx = 0.f, ly = 0.f;
+            if (!(p.flags & RT_FLAG_JITTER_OFF_)) { const float2 j = __ldg(&p.jitter[s_cur]); jx = j.x; jy = j.y; }
+            if (!(p.flags & RT_FLAG_LENS_OFF_)) { const float2 l = __ldg(&p.lens[s_cur + px + py]); lx = l.x; ly = l.y; }
+            const float u = (static_cast<float>(px) + jx) / static_cast<float>(p.W);     // spheres-app.cpp:149
+            const float v = (static_cast<float>(py) + jy) / static_cast<float>(p.H);     // :150
+            camera_get_ray(p.cam, u, v, lx, ly, o, d);
+            T = mk3(1.f, 1.f, 1.f); Lsum = mk3(0.f, 0.f, 0.f);
+            depth = 0; want_closest = true; want_shadow = false;
+            st = ST_IN_PATH;
+        }
+        const bool active = (st == ST_IN_PATH);
+
+        // ---- K2+K3: fused closest-hit / shadow query over every sphere ----
+        const QueryResult q = fused_query<NO_CULL>(sA, sB, sC, sR, p.n_groups, p.n_spheres, o, d, Ldir, active && want_closest, active && want_shadow);
+        ++n_pass;
+
+        // ---- K4: integrate ----
+        if (active) {
+            if (want_shadow) { ++n_shadow; if (!q.occluded) Lsum = Lsum + pend; }        // light.cpp:15-19
+            want_shadow = false;
+            if (want_closest) {
+                ++n_closest;
+                if (q.idx < 0) {                                                         // spheres-app.cpp:255
+                    Lsum = Lsum + T * sky;
+                    want_closest = false;
+                } else {
+                    const int idx = q.idx;
+                    const float* fa = reinterpret_cast<const float*>(sA) + (idx >> 1) * 4 + (idx & 1);
+                    const V3 ctr = mk3(fa[0], fa[2], reinterpret_cast<const float*>(sB)[(idx >> 1) * 4 + (idx & 1)]);
+                    const float radius = sR[idx];
+                    const V3 pos = mk3(q.t * d.x + o.x, q.t * d.y + o.y, q.t * d.z + o.z);   // ray-tracing.cpp:61
+                    const V3 n = (pos - ctr) / radius;                                   // :62
+                    const float tu = 0.5f * n.x + 0.5f, tv = 0.5f * n.z + 0.5f;          // :36-37
+                    const DevMat m = p.mats[idx];
+                    const bool cont = depth < p.max_depth;                               // spheres-app.cpp:247
+                    V3 atten = mk3(0.f, 0.f, 0.f), nd = d;
+                    bool scattered = false;
+                    if (cont) {
+                        float xi, u1, u2;
+                        rng_counter(static_cast<uint32_t>(pix), p.first_sample + static_cast<u64>(s_cur), static_cast<uint32_t>(depth), p.seed, xi, u1, u2);
+                        scattered = scatter(m, d, pos, n, tu, tv, xi, u1, u2, atten, nd);      // :246
+                    }
+                    if (has_light) { pend = T * direct_unshadowed(p, m, pos, n, tu, tv); want_shadow = true; }   // :250
+                    o = pos;
+                    if (cont && scattered) { T = T * atten; d = nd; ++depth; }           // :251
+                    else want_closest = false;
+                }
+            }
+            if (!want_closest && !want_shadow) {                                         // path complete
+                acc.x += Lsum.x * p.exposure; acc.y += Lsum.y * p.exposure; acc.z += Lsum.z * p.exposure;   // :182-183
+                acc.w += 1.0f;
+                ++n_paths;
+                if (++s_cur < s_end) st = ST_NEW_PATH;
+                else {
+                    if (p.n_chunks == 1) p.hdr[pix] = acc;
+                    else p.partial[static_cast<size_t>(chunk) * (static_cast<size_t>(p.W) * p.H) + pix] = acc;
+                    st = ST_NEED_ITEM;
+                }
+            }
+        }
+    }
+
+    // ---- stats: warp reduce, one atomic per warp ----
+    u64 c0 = n_closest, c1 = n_shadow, c3 = n_paths;
+    for (int off = 16; off > 0; off >>= 1) {
+        c0 += __shfl_down_sync(FULL, c0, off); c1 += __shfl_down_sync(FULL, c1, off); c3 += __shfl_down_sync(FULL, c3, off);
+    }
+    if (lane == 0) { atomicAdd(&p.stats[0], c0); atomicAdd(&p.stats[1], c1); atomicAdd(&p.stats[2], static_cast<u64>(n_pass)); atomicAdd(&p.stats[3], c3); }
+}
+
+// hdr[p] = ((hdr[p] + partial[0][p]) + partial[1][p]) + ...   (fixed order => deterministic)
+__global__ void rt_combine_kernel(float4* __restrict__ hdr, const float4* __restrict__ partial, int n_chunks, size_t n_pixels) {
+    const size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x;
+    if (i >= n_pixels) return;
+    float4 a = hdr[i];
+    for (int c = 0; c < n_chunks; ++c) {
+        const float4 b = partial[static_cast<size_t>(c) * n_pixels + i];
+        a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+    }
+    hdr[i] = a;
+}
+
+// K5 resolve, spheres-app.cpp:186-214.  16 B read + 4 B write per pixel (HBM-bound).
+__device__ __forceinline__ uint32_t store_color_channel(float x) {          // XMStoreColor: saturate, *255, round-to-nearest-even
+    float v = fminf(fmaxf(x, 0.0f), 1.0f);
+    v = v * 255.0f;
+    return static_cast<uint32_t>(__float2int_rn(v));
+}
+__global__ void rt_resolve_kernel(const float4* __restrict__ hdr, uint32_t* __restrict__ ldr, float n, size_t n_pixels) {
+    const float a = 2.51f, b = 0.03f, c = 2.43f, dd = 0.59f, e = 0.14f;
+    const float inv_gamma = 1 / 2.2f;
+    for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n_pixels; i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+        const float4 h = hdr[i];
+        float ch[3] = {h.x, h.y, h.z};
+        uint32_t out[3];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            float x = ch[k] / n;                                             // :201
+            x = saturate1((x * (a * x + b)) / (x * (c * x + dd) + e));      // :205
+            x = powf(x, inv_gamma);                                          // :208
+            out[k] = store_color_channel(x);                                 // :211
+        }
+        ldr[i] = 0xFF000000u | (out[0] << 16) | (out[1] << 8) | out[2];
+    }
+}
+
+// K6: primary-hit id buffers (jitter/lens per flags) for frame `first_sample`.
+template <bool NO_CULL>
+__global__ void __launch_bounds__(256) rt_primary_kernel(const RenderParams p, int32_t* __restrict__ sphere_idx, int32_t* __restrict__ material_id) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    float4 *sA, *sB; float2* sC; float* sR;
+    stage_scene(p, sA, sB, sC, sR, smem);
+    const u64 n_items = static_cast<u64>(p.tiles_x) * p.tiles_y * 32ull;
+    for (u64 item = blockIdx.x * static_cast<u64>(blockDim.x) + threadIdx.x; item < ((n_items + 31ull) & ~31ull); item += static_cast<u64>(gridDim.x) * blockDim.x) {
+        int chunk, px, py;
+        const bool valid = item < n_items && item_to_pixel(p, item, chunk, px, py);
+        V3 o = mk3(0.f, 0.f, 0.f), d = mk3(0.f, 0.f, 1.f);
+        if (valid) {
+            float jx = 0.f, jy = 0.f, lx = 0.f, ly = 0.f;
+            if (!(p.flags & RT_FLAG_JITTER_OFF_)) { const float2 j = __ldg(&p.jitter[0]); jx = j.x; jy = j.y; }
+            if (!(p.flags & RT_FLAG_LENS_OFF_)) { const float2 l = __ldg(&p.lens[px + py]); lx = l.x; ly = l.y; }
+            const float u = (static_cast<float>(px) + jx) / static_cast<float>(p.W);
+            const float v = (static_cast<float>(py) + jy) / static_cast<float>(p.H);
+            camera_get_ray(p.cam, u, v, lx, ly, o, d);
+        }
+        const QueryResult q = fused_query<NO_CULL>(sA, sB, sC, sR, p.n_groups, p.n_spheres, o, d, mk3(p.Lx, p.Ly, p.Lz), valid, false);
+        if (valid) {
+            const int pix = py * p.W + px;
+            if (sphere_idx) sphere_idx[pix] = q.idx;
+            if (material_id) material_id[pix] = q.idx >= 0 ? p.mats[q.idx].kind : 3;
+        }
+    }
+}
+
+}  // namespace rt

@@ -1,0 +1,151 @@
+/*
+ * rt_b200.h -- C ABI of the B200-native `src/spheres` path-tracing hot path.
+ *
+ * Drop-in boundary for SakibSaikia/CPURayTracer (citations relative to the reference tree):
+ * the reference has no FFI; its boundary is (i) the src/common-lib class surface that
+ * SpheresApp::InitScene / InitCamera construct (spheres-app.cpp:35-130) and (ii) the single
+ * call SpheresApp::DrawBitmap (spheres-app.cpp:163-222) that consumes them.  This header
+ * exports both as plain C: opaque handles, plain pointers and sizes, int status codes.
+ * include/rt_b200.hpp layers the reference's C++ class names on top of it.
+ *
+ * Every function returns RT_OK (0) or an rt_status error; rt_last_error() holds the message.
+ * There is NO CPU fallback: if no CUDA device / kernel image is usable the call fails loudly.
+ * A context is not re-entrant: drive it from one host thread (as the reference's UI thread does).
+ */
+#ifndef RT_B200_H
+#define RT_B200_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(_WIN32)
+#define RT_API __declspec(dllexport)
+#else
+#define RT_API __attribute__((visibility("default")))
+#endif
+
+typedef enum rt_status {
+    RT_OK = 0,
+    RT_ERR_INVALID_ARGUMENT = 1,
+    RT_ERR_CUDA = 2,
+    RT_ERR_OUT_OF_MEMORY = 3,
+    RT_ERR_NOT_READY = 4,       /* scene / camera / framebuffer not set */
+    RT_ERR_UNSUPPORTED = 5
+} rt_status;
+
+/* ---- flat scene description, version 1 (what rt_scene_export returns) ---------------------
+ * Colours are the floats AFTER the reference's 8-bit XMCOLOR round trip
+ * (XMCOLOR(float x4) ctor -> XMLoadColor; texture.cpp:5,16-17, light.cpp:8). */
+typedef struct rt_sphere_desc   { float cx, cy, cz, radius; int32_t material; } rt_sphere_desc;            /* ray-tracing.h:53-58 */
+typedef struct rt_material_desc { int32_t kind; int32_t texture; float smoothness; float ior; } rt_material_desc; /* material.h */
+typedef struct rt_texture_desc  { int32_t kind; float tiling; float c0[4]; float c1[4]; } rt_texture_desc;    /* texture.h */
+typedef struct rt_light_desc    { float dir[3]; float color[4]; float luminance; } rt_light_desc;            /* light.h:15-21, dir normalised */
+
+/* material ids (also the values written to the primary-hit material buffer) */
+enum { RT_MAT_OPAQUE = 0,        /* DielectricOpaque,       material.h:37-52 */
+       RT_MAT_METAL = 1,         /* Metal,                  material.h:21-35 */
+       RT_MAT_TRANSPARENT = 2,   /* DielectricTransparent,  material.h:54-68 */
+       RT_MAT_SKY = 3 };         /* Emissive sky on a miss, material.h:70-84, spheres-app.cpp:255 */
+enum { RT_TEX_CONST = 0, RT_TEX_CHECKER = 1 };   /* texture.h:12-30 */
+
+/* Camera(origin, lookAt, verticalFOV, aspectRatio, focalLength, aperture), camera.h:9 */
+typedef struct rt_camera_params {
+    float origin[3]; float look_at[3]; float vfov_deg; float aspect; float focus; float aperture;
+} rt_camera_params;
+/* what the constructor derives (camera.cpp:14-27): m_origin, m_x, m_y, m_originImagePlane */
+typedef struct rt_camera_basis { float origin[3], x[3], y[3], image_origin[3]; float aperture, focus; } rt_camera_basis;
+
+/* render flags */
+enum { RT_FLAG_JITTER_OFF = 1u,   /* jitterOffset = 0 (spheres-app.cpp:140)              */
+       RT_FLAG_LENS_OFF = 2u };   /* lens offset = 0  (spheres-app.cpp:152): pinhole rays */
+
+typedef struct rt_stats {
+    uint64_t paths;            /* path samples traced since the last rt_stats_reset            */
+    uint64_t closest_rays;     /* closest-hit queries (GetClosestIntersection, spheres-app.cpp:224) */
+    uint64_t shadow_rays;      /* occlusion queries (light.cpp:13-15)                          */
+    uint64_t sphere_tests;     /* n_spheres * (closest_rays + shadow_rays)                     */
+    uint64_t passes;           /* warp-level fused passes executed (diagnostic)                */
+    double   render_ms;        /* CUDA-event time of the render kernels since the last reset   */
+    double   resolve_ms;       /* CUDA-event time of the resolve kernels                       */
+    int32_t  sm_count;         /* multiProcessorCount of the device                            */
+    int32_t  clock_khz;        /* cudaDevAttrClockRate                                          */
+    int32_t  launches;         /* kernels launched since the last reset                        */
+    int32_t  reserved;
+} rt_stats;
+
+typedef struct rt_context rt_context;   /* one GPU, one stream, one framebuffer */
+typedef struct rt_scene   rt_scene;     /* host-side scene recorder            */
+
+/* ---- context ---- */
+RT_API int  rt_context_create(int device, rt_context** out);
+RT_API void rt_context_destroy(rt_context* ctx);
+RT_API const char* rt_last_error(void);                        /* thread-local message of the last failure */
+RT_API int  rt_set_stream(rt_context* ctx, void* cuda_stream); /* borrow a cudaStream_t (e.g. torch's current stream) */
+RT_API int  rt_synchronize(rt_context* ctx);
+
+/* ---- scene recorder: mirrors the reference constructors ---- */
+RT_API int  rt_scene_create(rt_scene** out);
+RT_API void rt_scene_destroy(rt_scene* scene);
+/* ConstTexture(XMCOLOR) texture.cpp:3-6 -- rgba in [0,1] is quantised to 8 bit exactly as XMCOLOR does. Returns id >= 0, or -rt_status. */
+RT_API int  rt_scene_add_texture_const(rt_scene* s, const float rgba[4]);
+/* CheckerTexture(XMCOLOR, XMCOLOR, tiling) texture.cpp:13-18 */
+RT_API int  rt_scene_add_texture_checker(rt_scene* s, const float rgba0[4], const float rgba1[4], float tiling);
+/* DielectricOpaque(albedo, smoothness) material.cpp:15-18;  Metal(reflectance, smoothness) :67-70;
+ * DielectricTransparent(smoothness, ior) :105-109.  Return material id >= 0, or -rt_status. */
+RT_API int  rt_scene_add_material_opaque(rt_scene* s, int texture, float smoothness);
+RT_API int  rt_scene_add_material_metal(rt_scene* s, int texture, float smoothness);
+RT_API int  rt_scene_add_material_transparent(rt_scene* s, float smoothness, float ior);
+/* Sphere(center, radius, material) ray-tracing.cpp:21-24. Returns the sphere index (insertion order). */
+RT_API int  rt_scene_add_sphere(rt_scene* s, const float center[3], float radius, int material);
+/* Emissive(luminance, texture) as m_skyMaterial, spheres-app.cpp:120-121 */
+RT_API int  rt_scene_set_sky(rt_scene* s, float luminance, int texture);
+/* DirectionalLight(dir, XMCOLOR, luminance, occlusionTest) light.cpp:4-9; the occlusion callback is the scene itself. */
+RT_API int  rt_scene_add_directional_light(rt_scene* s, const float dir[3], const float rgba[4], float luminance);
+/* flat access (byte-identical input for an external checker) */
+RT_API int  rt_scene_counts(const rt_scene* s, int32_t* n_spheres, int32_t* n_materials, int32_t* n_textures, int32_t* n_lights);
+RT_API int  rt_scene_export(const rt_scene* s, rt_sphere_desc* spheres, rt_material_desc* materials, rt_texture_desc* textures,
+                            rt_light_desc* lights, float* sky_luminance, int32_t* sky_texture);
+/* load already-quantised flat arrays (e.g. a frozen scene file); replaces the recorder's content */
+RT_API int  rt_scene_import(rt_scene* s, int32_t n_spheres, const rt_sphere_desc* spheres, int32_t n_materials, const rt_material_desc* materials,
+                            int32_t n_textures, const rt_texture_desc* textures, int32_t n_lights, const rt_light_desc* lights,
+                            float sky_luminance, int32_t sky_texture);
+
+/* ---- binding to a context (uploads to HBM) ---- */
+RT_API int  rt_set_scene(rt_context* ctx, const rt_scene* scene);            /* InitScene: spheres-app.cpp:51-130 */
+RT_API int  rt_set_camera(rt_context* ctx, const rt_camera_params* cam);     /* InitCamera: spheres-app.cpp:35-49 */
+RT_API int  rt_camera_basis_of(const rt_camera_params* cam, rt_camera_basis* out);   /* Camera::Camera, camera.cpp:3-28 (host only) */
+RT_API int  rt_set_exposure(rt_context* ctx, float stops);                   /* m_exposure, default -15: spheres-app.cpp:48 */
+RT_API int  rt_set_seed(rt_context* ctx, uint32_t seed);                     /* counter-RNG stream selector, default 0 */
+RT_API int  rt_set_chunk_spp(rt_context* ctx, int chunk_spp);                /* 0 = auto; samples per work item (load balance) */
+/* InitBuffers (app.cpp:112-119): allocate W*H float4 running-sum + BGRA8 buffers, zero-filled. */
+RT_API int  rt_framebuffer_resize(rt_context* ctx, int width, int height);
+RT_API int  rt_framebuffer_clear(rt_context* ctx);
+
+/* ---- the hot path ----
+ * rt_render == `spp` consecutive SpheresApp::DrawBitmap() calls (spheres-app.cpp:163-184) starting at
+ * m_sampleCount == first_sample (>= 1), with AppSettings::k_recursionDepth == max_depth.
+ * Adds to the running sum; asynchronous on the context's stream. */
+RT_API int  rt_render(rt_context* ctx, uint64_t first_sample, int spp, int max_depth, uint32_t flags);
+/* m_backbufferHdr (app.h:26): float4 per pixel, row-major j*W+i, row 0 = top; xyz = sum of exposure-scaled
+ * samples, w = number of samples accumulated. */
+RT_API int  rt_read_hdr_sum(rt_context* ctx, float* rgba, size_t n_pixels);
+RT_API int  rt_write_hdr_sum(rt_context* ctx, const float* rgba, size_t n_pixels);   /* resume from a checkpoint */
+/* Resolve (spheres-app.cpp:186-214): sum / sample_count, ACES fit, gamma 1/2.2, XMStoreColor -> 0xAARRGGBB.
+ * bgra8 may be NULL to only run the kernel (result stays in HBM). */
+RT_API int  rt_resolve_ldr(rt_context* ctx, uint64_t sample_count, uint32_t* bgra8, size_t n_pixels);
+/* Primary-hit id buffers for frame `sample`: sphere index (-1 = miss) and material id (RT_MAT_*). */
+RT_API int  rt_primary_hits(rt_context* ctx, uint64_t sample, uint32_t flags, int32_t* sphere_idx, int32_t* material_id, size_t n_pixels);
+
+/* ---- interop / instrumentation ---- */
+RT_API void* rt_hdr_device_ptr(rt_context* ctx);                   /* float4[W*H] in HBM (e.g. for an NCCL reduce) */
+RT_API int  rt_hdr_bind_external(rt_context* ctx, void* device_ptr); /* render into a caller-owned device buffer (NULL = own buffer) */
+RT_API int  rt_get_stats(rt_context* ctx, rt_stats* out);          /* synchronises the stream */
+RT_API int  rt_stats_reset(rt_context* ctx);
+RT_API const char* rt_build_info(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RT_B200_H */
