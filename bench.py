@@ -1,0 +1,325 @@
+#!/usr/bin/env python
+"""bench.py -- path samples/s of the B200 `src/spheres` render loop (BASELINE.json metric).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c1..c5] [--spp-step S] [--impl reference]
+
+One "step" = one pass of the hot path: `spp_per_step` x SpheresApp::DrawBitmap (spheres-app.cpp:163-184) over
+every pixel of the workload, i.e. one rt_render() call per GPU (+ the sum-reduce onto rank 0 when N > 1).
+Default workload c3 = BASELINE.json configs[2] (default 488-sphere scene, 1920x1080, depth 50: the full path with
+indirect light, Fresnel glass and the reference's hemisphere sampler); configs[1] (direct only) is `--workload c2`.
+N > 1: launched by torchrun, one rank per GPU; every rank renders `spp_per_step` frames of a disjoint sample
+range (weak scaling), buffers are combined with ncclReduce.  Rank 0 prints ONE JSON line.
+
+`--impl reference` times the reference's own CPU algorithm (per-material atomic Halton counters, BVH, recursive
+integrator, all host threads) -- the oracle port, because the reference itself needs Windows/DirectXMath.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+# name -> (scene, width, height, max_depth, config spp, description)
+WORKLOADS = {
+    "c1": ("d488", 1280, 720, 50, 256, "configs[0]: default scene 1280x720 depth 50 (reference defaults; 256 spp chosen)"),
+    "c2": ("d488", 1920, 1080, 0, 256, "configs[1]: default scene, direct lighting only (1 vertex), 1920x1080, 256 spp"),
+    "c3": ("d488", 1920, 1080, 50, 1024, "configs[2]: default scene, indirect + Fresnel glass, depth 50, 1920x1080, 1024 spp"),
+    "c4": ("d488", 3840, 2160, 50, 1024, "configs[3]: default scene, thin lens aperture 0.4, 3840x2160, 1024 spp"),
+    "c5": ("s4096", 3840, 2160, 50, 4096, "configs[4]: 4096-sphere scene, 3840x2160, 4096 spp, sample-split + ncclReduce"),
+}
+FLOP_PER_TEST = 17.0            # irreducible FP32 flops of one ray-sphere discriminant test
+FP32_PEAK_MEASURED_TFLOPS = 72.5   # FFMA-chain microbenchmark on this pool's B200 (profiles/r01_fp32_peak.txt)
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=4)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
+    ap.add_argument("--spp-step", type=int, default=0, help="frames per step per GPU (0 = 256, or 32 for c5)")
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------------------------ CPU arm (oracle)
+def oracle_setup(workload):
+    """Scene + camera of the workload as flat arrays for the oracle.  The flat scene comes from the product's host
+    recorder (pure host code); the oracle is the thing timed here, never the other way round."""
+    import cpuraytracer_b200 as rt
+    from oracle import orc
+    scene_name, w, h, depth, _, _ = WORKLOADS[workload]
+    scene = rt.scenes.NAMED[scene_name]()
+    cam = rt.scenes.default_camera(aspect=w / h)
+    osc = orc.Scene.from_flat(scene.export())
+    cp = orc.camera_params(cam.origin, cam.look_at, cam.vertical_fov, cam.aspect_ratio, cam.focal_length, cam.aperture)
+    return orc, osc, cp, (w, h, depth)
+
+
+def oracle_reference_cfg(orc, w, h, depth, first, spp):
+    """The reference's configuration: shared atomic Halton counters (material.h:34,50-51,67), BVH
+    (ray-tracing.cpp:107-214), recursive GetHitColor (spheres-app.cpp:238-257), all hardware threads."""
+    return orc.config(w, h, spp=spp, max_depth=depth, first_sample=first, rng_mode=orc.RNG_HALTON,
+                      accel=orc.ACCEL_BVH, integrator=orc.INTEGRATOR_RECURSIVE, threads=0)
+
+
+def cpu_baseline(workload, budget_s):
+    """Bounded sample: whole frames (1 spp over every pixel of the workload) until ~budget_s of CPU time."""
+    import numpy as np
+    orc, osc, cp, (w, h, depth) = oracle_setup(workload)
+    cores = os.cpu_count() or 1
+    hdr = np.zeros((h, w, 4), np.float32)
+    t0 = time.perf_counter()
+    frames, paths = 0, 0
+    while True:
+        _, st = orc.render(osc, cp, oracle_reference_cfg(orc, w, h, depth, frames + 1, 1), hdr)
+        frames += 1
+        paths += st.paths
+        el = time.perf_counter() - t0
+        if el >= budget_s or el + el / frames > 2.5 * budget_s:
+            break
+    return {"value": paths / el, "unit": "path samples/s", "cores": cores, "kind": "port",
+            "sample": f"{frames} full frame(s) (1 spp each, {w}x{h}, depth {depth}) of the workload in {el:.1f} s; oracle in the "
+                      f"reference configuration (atomic Halton counters + BVH + recursive integrator, g++ -O2, {cores} threads)"}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    scene_name, w, h, depth, cfg_spp, desc = WORKLOADS[args.workload]
+    import numpy as np
+    orc, osc, cp, _ = oracle_setup(args.workload)
+    cores = os.cpu_count() or 1
+    hdr = np.zeros((h, w, 4), np.float32)
+    frame = 0
+    for _ in range(args.warmup):
+        frame += 1
+        orc.render(osc, cp, oracle_reference_cfg(orc, w, h, depth, frame, 1), hdr)
+    t0 = time.perf_counter()
+    paths = 0
+    for _ in range(args.steps):
+        frame += 1
+        _, st = orc.render(osc, cp, oracle_reference_cfg(orc, w, h, depth, frame, 1), hdr)
+        paths += st.paths
+    el = time.perf_counter() - t0
+    value = paths / el
+    sample = f"each step = 1 full frame (1 spp, {w}x{h}, depth {depth}) on {cores} host threads"
+    line = {"impl": "reference", "metric": "path samples/s", "value": value, "unit": "path samples/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * el / max(args.steps, 1), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"{args.workload} {desc}", "scene": scene_name, "width": w, "height": h, "max_depth": depth,
+                       "spp_per_step": 1, "note": "reference needs Windows SDK + DirectXMath (absent): oracle port in the reference's "
+                       "configuration (atomic Halton + BVH + recursive), g++ -O2"},
+            "cpu_baseline": {"value": value, "unit": "path samples/s", "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": value, "unit": "path samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+# ------------------------------------------------------------------------------------------------ clocks
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.idx, self.proc, self.path = gpu_index, None, None
+
+    def start(self):
+        try:
+            f = tempfile.NamedTemporaryFile("w", suffix=".csv", delete=False)
+            self.path = f.name
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.idx), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=f, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.proc is None:
+            return out
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        try:
+            rows = [r.strip().split(", ") for r in open(self.path) if r.strip()]
+            os.unlink(self.path)
+        except Exception:
+            return out
+        sm, mx, power, reasons = [], [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in rows:
+            if len(r) < 9:
+                continue
+            try:
+                sm.append(float(r[1])); mx.append(float(r[2])); power.append(float(r[3]))
+            except ValueError:
+                continue
+            for k, nm in enumerate(names):
+                if r[5 + k].strip().lower().startswith("active"):
+                    reasons.add(nm)
+        if sm:
+            out.update(sm_mhz=statistics.median(sm), sm_max_mhz=max(mx), reasons=sorted(reasons), samples=len(sm),
+                       power_w_max=max(power))
+        return out
+
+
+# ------------------------------------------------------------------------------------------------ B200 arm
+def run_b200(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    import cpuraytracer_b200 as rt
+    from cpuraytracer_b200.distributed import ShardedRenderer
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; cpuraytracer_b200 has no CPU fallback (use --impl reference for the CPU arm)")
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        raise SystemExit(f"bench.py: --gpus {args.gpus} but WORLD_SIZE={world}; launch N > 1 with torch.distributed.run")
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
+
+    scene_name, w, h, depth, cfg_spp, desc = WORKLOADS[args.workload]
+    spp_step = args.spp_step or (32 if args.workload == "c5" else 256)
+    n_pix = w * h
+    scene = rt.scenes.NAMED[scene_name]()
+    flat = scene.export()
+    cam = rt.scenes.default_camera(aspect=w / h)
+    sr = ShardedRenderer(w, h, device=local)
+    r = sr.renderer
+    sr.set_scene(scene)
+    sr.set_camera(cam)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=f"cuda:{local}")      # > 126 MB L2
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step(i):
+        # global frame range of step i: [1 + i*world*spp_step, ...); each rank takes its disjoint share
+        sr.render(world * spp_step, depth, 0, first_sample=1 + i * world * spp_step, reduce=True)
+
+    # ---- warm-up ----
+    for i in range(args.warmup):
+        step(i)
+    barrier()
+    sr.clear()
+    r.reset_stats()
+
+    # ---- timed region: exactly K steps, CUDA events on the launching stream, L2 flushed between steps ----
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    barrier()
+    t_wall0 = time.perf_counter()
+    for i in range(args.steps):
+        flush.fill_(i & 0xFF)
+        ev[i][0].record()
+        step(i)
+        ev[i][1].record()
+    barrier()
+    t_wall = time.perf_counter() - t_wall0
+    clocks = sampler.stop() if rank == 0 else None
+    ms_steps = [a.elapsed_time(b) for a, b in ev]
+    total_ms = torch.tensor([sum(ms_steps)], dtype=torch.float64, device=f"cuda:{local}")
+    st = r.stats()
+    counts = torch.tensor([st.paths, st.closest_rays, st.shadow_rays, st.sphere_tests, st.launches], dtype=torch.float64, device=f"cuda:{local}")
+    kern_ms = torch.tensor([st.render_ms], dtype=torch.float64, device=f"cuda:{local}")
+    if world > 1:
+        dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
+        dist.all_reduce(kern_ms, op=dist.ReduceOp.MAX)
+        dist.all_reduce(counts, op=dist.ReduceOp.SUM)
+    total_s = float(total_ms.item()) * 1e-3
+    paths = world * spp_step * n_pix * args.steps
+    assert int(counts[0].item()) == paths, (int(counts[0].item()), paths)
+    value = paths / total_s
+    # sanity: rank 0 holds the whole job's sum -> every pixel accumulated K * world * spp_step samples
+    if rank == 0:
+        wsum = float(sr.hdr[..., 3].double().mean().item())
+        assert abs(wsum - args.steps * world * spp_step) < 1e-3 * wsum, wsum
+
+    # ---- end to end through the public API with HOST buffers: scene arrays -> rt_scene_import/rt_set_scene (H2D),
+    #      render (+ reduce), running-sum buffer -> pinned host memory (D2H) ----
+    host_hdr = torch.empty((h, w, 4), dtype=torch.float32).pin_memory()
+    h2d = flat.spheres.nbytes + flat.materials.nbytes + flat.textures.nbytes + flat.lights.nbytes + 40
+    d2h = host_hdr.numel() * 4
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        sc = rt.Scene.from_flat(flat)               # host arrays in, as a caller of the C ABI would hand them over
+        sr.set_scene(sc)
+        sr.set_camera(cam)
+        sr.clear()
+        step(i)
+        if rank == 0:
+            host_hdr.copy_(sr.hdr, non_blocking=True)
+        torch.cuda.synchronize()
+    barrier()
+    e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=f"cuda:{local}")
+    if world > 1:
+        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+    e2e_value = paths / float(e2e_s.item())
+
+    if rank == 0:
+        kern_s = float(kern_ms.item()) * 1e-3
+        tests = float(counts[3].item())
+        achieved = tests * FLOP_PER_TEST / kern_s / 1e12 / world            # per-GPU TFLOP/s of the render kernel
+        line = {
+            "metric": "path samples/s", "value": value, "unit": "path samples/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * total_s / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"{args.workload} {desc}", "scene": scene_name, "n_spheres": int(len(flat.spheres)), "width": w,
+                       "height": h, "max_depth": depth, "spp_per_step_per_gpu": spp_step, "config_spp": cfg_spp,
+                       "partition": "disjoint sample ranges per GPU + ncclReduce(sum) to rank 0" if world > 1 else "single GPU",
+                       "l2": "flushed between timed steps (256 MiB fill); scene lives in shared memory"},
+            "rays_per_s": (float(counts[1].item()) + float(counts[2].item())) / total_s,
+            "rays_per_path": (float(counts[1].item()) + float(counts[2].item())) / paths,
+            "gpu_launches": int(counts[4].item()),
+            "e2e": {"value": e2e_value, "unit": "path samples/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
+            "roofline": {"bound": "fp32", "achieved": achieved, "peak": FP32_PEAK_MEASURED_TFLOPS, "unit": "TFLOP/s",
+                         "frac": achieved / FP32_PEAK_MEASURED_TFLOPS, "traffic": None,
+                         "note": "rt_render_kernel: sphere tests x 17 flop / kernel time (cudaEvents on its stream); peak = measured "
+                                 "FFMA-chain FP32 rate (MEASURED_PEAKS.json has no FP32 figure; nominal 148x128x2x1.965 GHz = 74.5)",
+                         "sphere_tests_per_s": tests / kern_s / world, "kernel_ms_per_step": 1e3 * kern_s / args.steps},
+            "clocks": clocks, "wall_s": t_wall,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline(args.workload, args.cpu_seconds)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_b200(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

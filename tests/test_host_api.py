@@ -1,0 +1,160 @@
+"""CPU-side checks of the drop-in boundary: the C-ABI library loads, exports every symbol include/rt_b200.h
+declares, the scene recorder flattens the reference constructors exactly, and errors are loud."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+from conftest import ROOT, orc_camera
+
+
+def _declared_symbols():
+    src = open(os.path.join(ROOT, "include", "rt_b200.h")).read()
+    return sorted(set(re.findall(r"RT_API\s+[\w\s\*]+?\b(rt_\w+)\s*\(", src)))
+
+
+def test_library_exports_every_declared_symbol(rt):
+    lib = rt.load()
+    names = _declared_symbols()
+    assert len(names) >= 30
+    for n in names:
+        assert hasattr(lib, n), f"librt_b200.so does not export {n}"
+    from cpuraytracer_b200 import _lib
+    assert sorted(s[0] for s in _lib.SYMBOLS) == names      # the ctypes table covers the header exactly
+    assert b"sm_100a" in lib.rt_build_info()
+
+
+def test_library_is_sm100a_only(rt):
+    import shutil
+    import subprocess
+    cuobjdump = shutil.which("cuobjdump") or "/usr/local/cuda/bin/cuobjdump"
+    if not os.path.exists(cuobjdump):
+        pytest.skip("cuobjdump not available")
+    out = subprocess.run([cuobjdump, "-lelf", rt.LIB_PATH], capture_output=True, text=True).stdout
+    archs = set(re.findall(r"sm_\d+a?", out))
+    assert archs == {"sm_100a"}, archs
+
+
+def test_no_cpu_fallback(rt):
+    """Without a CUDA device the compute API must fail loudly (this container has none)."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("CUDA device present")
+    with pytest.raises(rt.RtError) as e:
+        rt.Renderer(width=8, height=8)
+    assert "no CPU fallback" in str(e.value)
+
+
+def test_product_never_imports_oracle():
+    """The oracle is test infrastructure: nothing under cpuraytracer_b200/ or include/ may reference it."""
+    for base in ("cpuraytracer_b200", "include"):
+        for dp, _, fns in os.walk(os.path.join(ROOT, base)):
+            for fn in fns:
+                if fn.endswith((".py", ".cu", ".cuh", ".h", ".hpp", ".cpp")):
+                    txt = open(os.path.join(dp, fn), errors="replace").read()
+                    assert "rt_oracle" not in txt and "liborc" not in txt and "from oracle" not in txt and "import oracle" not in txt, fn
+
+
+def test_scene_recorder_counts_and_ids(rt):
+    s = rt.scenes.scene_d488()
+    ns, nm, nt, nl = s.counts()
+    assert (ns, nm, nl) == (488, 488, 1)          # each Sphere owns its material (ray-tracing.h:57)
+    flat = s.export()
+    sp = flat.spheres
+    # insertion order of InitScene (spheres-app.cpp:60-114)
+    assert tuple(sp[0])[:4] == (0.0, -1000.0, 0.0, 1000.0)
+    assert tuple(sp[485])[:4] == (0.0, 1.0, 0.0, 1.0) and flat.materials[sp[485]["material"]]["kind"] == rt.RT_MAT_TRANSPARENT
+    assert tuple(sp[486])[:4] == (-4.0, 1.0, 0.0, 1.0) and flat.materials[sp[486]["material"]]["kind"] == rt.RT_MAT_OPAQUE
+    assert tuple(sp[487])[:4] == (4.0, 1.0, 0.0, 1.0) and flat.materials[sp[487]["material"]]["kind"] == rt.RT_MAT_METAL
+    small = sp[1:485]
+    assert np.all(small["radius"] == np.float32(0.2)) and np.all(small["cy"] == np.float32(0.2))
+    a = np.repeat(np.arange(-11, 11), 22)
+    b = np.tile(np.arange(-11, 11), 22)
+    assert np.all((small["cx"] >= a) & (small["cx"] < a + 0.9001)) and np.all((small["cz"] >= b) & (small["cz"] < b + 0.9001))
+    kinds = flat.materials[small["material"]]["kind"]
+    frac = [np.mean(kinds == k) for k in (0, 1, 2)]
+    assert 0.7 < frac[0] < 0.9 and 0.08 < frac[1] < 0.22 and 0.01 < frac[2] < 0.1     # 80 / 15 / 5 % recipe
+    assert flat.sky_luminance == 8000.0 and flat.lights[0]["luminance"] == 40000.0
+    assert np.allclose(flat.lights[0]["dir"], 1 / np.sqrt(3))
+
+
+def test_scene_is_reproducible_and_s4096(rt):
+    a, b = rt.scenes.scene_d488().export(), rt.scenes.scene_d488().export()
+    assert a.spheres.tobytes() == b.spheres.tobytes() and a.textures.tobytes() == b.textures.tobytes()
+    assert rt.scenes.scene_s4096().counts()[0] == 4096
+
+
+def test_colours_are_xmcolor_quantised(rt, orc):
+    """XMCOLOR(float x4) -> XMLoadColor round trip (texture.cpp:5,16-17; light.cpp:8): floats are k * (1/255)."""
+    flat = rt.scenes.scene_d488().export()
+    L = orc.load()
+    for arr in (flat.textures["c0"], flat.textures["c1"], flat.lights["color"]):
+        k = np.rint(arr.astype(np.float64) * 255).astype(int)
+        assert np.array_equal(arr, (k.astype(np.float32) * np.float32(1.0 / 255.0)))
+    ground = flat.textures[flat.materials[flat.spheres[0]["material"]]["texture"]]
+    assert ground["kind"] == 1 and ground["tiling"] == 2500.0
+    exp0 = [L.orc_xmcolor_load(L.orc_xmcolor_quantize(v)) for v in (0.9, 0.9, 0.9, 1.0)]
+    exp1 = [L.orc_xmcolor_load(L.orc_xmcolor_quantize(v)) for v in (0.2, 0.3, 0.1, 1.0)]
+    assert list(ground["c0"]) == exp0 and list(ground["c1"]) == exp1
+    assert [int(round(v * 255)) for v in exp0[:3]] == [230, 230, 230] and [int(round(v * 255)) for v in exp1[:3]] == [51, 76, 26]   # 0.3f*255 rounds to 76.5 in fp32 -> ties-to-even 76
+    sky = flat.textures[flat.sky_texture]
+    assert [int(round(v * 255)) for v in sky["c0"][:3]] == [217, 232, 250]
+
+
+def test_camera_basis_matches_oracle(rt, orc):
+    for cam in (rt.scenes.default_camera(), rt.Camera((1, 2, 3), (-4, 0.5, 9), 60.0, 1.0, 5.0, 0.1)):
+        b = cam.basis()
+        oc = orc.OrcCamera()
+        cp = orc_camera(orc, cam)
+        orc.load().orc_camera_make(C.byref(cp), C.byref(oc))
+        for f in ("origin", "x", "y", "image_origin"):
+            assert list(getattr(b, f)) == list(getattr(oc, f)), f
+        assert b.aperture == oc.aperture and b.focus == oc.focus
+    assert abs(rt.scenes.default_camera().focal_length - np.sqrt(151.25)) < 1e-5     # |origin - lookAt|, spheres-app.cpp:45
+
+
+def test_recorder_error_behaviour(rt):
+    s = rt.Scene()
+    with pytest.raises(rt.RtError) as e:
+        s._lib.rt_scene_add_sphere.restype  # noqa: B018  (symbol exists)
+        from cpuraytracer_b200 import _lib
+        _lib.check_id(s._lib.rt_scene_add_sphere(s.handle, (C.c_float * 3)(0, 0, 0), 1.0, 5))
+    assert e.value.code == 1 and "material id 5" in str(e.value)
+    from cpuraytracer_b200 import _lib
+    with pytest.raises(rt.RtError):
+        _lib.check_id(s._lib.rt_scene_add_material_opaque(s.handle, 3, 16.0))          # texture out of range
+    with pytest.raises(rt.RtError):
+        _lib.check_id(s._lib.rt_scene_add_material_transparent(s.handle, 16.0, 0.0))   # ior must be > 0
+    t = s.add_texture(rt.ConstTexture(rt.XMCOLOR(1, 1, 1)))
+    m = _lib.check_id(s._lib.rt_scene_add_material_opaque(s.handle, t, 16.0))
+    with pytest.raises(rt.RtError):
+        _lib.check_id(s._lib.rt_scene_add_sphere(s.handle, (C.c_float * 3)(0, 0, 0), -1.0, m))   # radius <= 0
+    with pytest.raises(rt.RtError):
+        _lib.check(s._lib.rt_scene_add_directional_light(s.handle, (C.c_float * 3)(0, 0, 0), (C.c_float * 4)(1, 1, 1, 1), 1.0))
+    with pytest.raises(TypeError):
+        s.add(rt.Sphere((0, 0, 0), 1.0, rt.Emissive(1.0, rt.ConstTexture(rt.XMCOLOR(1, 1, 1)))))
+
+
+def test_flat_scene_round_trip(rt, tmp_path):
+    flat = rt.scenes.scene_small().export()
+    p = str(tmp_path / "scene.npz")
+    flat.save(p)
+    back = rt.Scene.from_flat(rt.FlatScene.load(p)).export()
+    for f in ("spheres", "materials", "textures", "lights"):
+        assert getattr(flat, f).tobytes() == getattr(back, f).tobytes()
+    assert (flat.sky_luminance, flat.sky_texture) == (back.sky_luminance, back.sky_texture)
+
+
+def test_image_sinks(rt, tmp_path):
+    bgra = np.array([[0xFF102030, 0xFFFFFFFF]], np.uint32)
+    p = str(tmp_path / "a.ppm")
+    rt.write_ppm(p, bgra)
+    raw = open(p, "rb").read()
+    assert raw.startswith(b"P6\n2 1\n255\n") and raw[-6:] == bytes([0x10, 0x20, 0x30, 255, 255, 255])
+    hdr = np.ones((2, 3, 4), np.float32) * 4
+    q = str(tmp_path / "a.pfm")
+    rt.write_pfm(q, hdr, 4)
+    raw = open(q, "rb").read()
+    assert raw.startswith(b"PF\n3 2\n-1.0\n") and np.frombuffer(raw[-72:], "<f4").tolist() == [1.0] * 18
