@@ -237,7 +237,7 @@ struct rt_context {
     std::vector<EventPair> pending; std::vector<EventPair> pool;
     double render_ms = 0, resolve_ms = 0; int launches = 0;
     u64 stat_base[4] = {0, 0, 0, 0};
-    int render_blocks_per_sm = 0;
+    int render_blocks_per_sm = 0, tpb = 256;
 
     float4* hdr() const { return hdr_ext ? hdr_ext : hdr_own; }
 };
@@ -270,6 +270,8 @@ template <class T> static int dev_realloc(T*& p, size_t n) {
     return RT_OK;
 }
 static size_t scene_smem_bytes(int n_pad) { return static_cast<size_t>(n_pad / 2) * 40u + static_cast<size_t>(n_pad) * 4u; }
+// scene arrays + the per-thread candidate lists (2 lists x RT_LIST_CAP words), see stage_scene()
+static size_t cta_smem_bytes(int n_pad, int tpb) { return scene_smem_bytes(n_pad) + static_cast<size_t>(tpb) * 2u * RT_LIST_CAP * 4u; }
 
 extern "C" {
 
@@ -338,8 +340,8 @@ int rt_set_scene(rt_context* c, const rt_scene* s) {
     const int n = static_cast<int>(s->spheres.size());
     const int n_pad = std::max(32, (n + 31) / 32 * 32);
     const int np = n_pad / 2;
-    if (scene_smem_bytes(n_pad) > static_cast<size_t>(c->prop.sharedMemPerBlockOptin))
-        return fail(RT_ERR_UNSUPPORTED, "rt_set_scene: %d spheres need %zu B of shared memory per CTA, device limit is %zu", n, scene_smem_bytes(n_pad), static_cast<size_t>(c->prop.sharedMemPerBlockOptin));
+    if (cta_smem_bytes(n_pad, 256) > static_cast<size_t>(c->prop.sharedMemPerBlockOptin))
+        return fail(RT_ERR_UNSUPPORTED, "rt_set_scene: %d spheres need %zu B of shared memory per CTA, device limit is %zu", n, cta_smem_bytes(n_pad, 256), static_cast<size_t>(c->prop.sharedMemPerBlockOptin));
     const bool has_light = !s->lights.empty();
     double L[3] = {0, 0, 0};
     if (has_light) for (int k = 0; k < 3; ++k) L[k] = s->lights[0].dir[k];
@@ -398,16 +400,24 @@ int rt_set_scene(rt_context* c, const rt_scene* s) {
     const float* sc = sky.c0;                                             // checker at (0,0): u%2 == v%2 -> colour 0
     b.skyx = s->sky_luminance * sc[0]; b.skyy = s->sky_luminance * sc[1]; b.skyz = s->sky_luminance * sc[2];
     c->n_spheres = n; c->n_pad = n_pad; c->scene_set = true;
-    // opt in to large dynamic shared memory and size the persistent grid
-    const size_t smem = scene_smem_bytes(n_pad);
-    RT_CUDA(cudaFuncSetAttribute(rt::rt_render_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-    RT_CUDA(cudaFuncSetAttribute(rt::rt_render_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-    RT_CUDA(cudaFuncSetAttribute(rt::rt_primary_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-    RT_CUDA(cudaFuncSetAttribute(rt::rt_primary_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-    int bps = 0;
-    RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, rt::rt_render_kernel<false>, 256, smem));
-    if (bps < 1) return fail(RT_ERR_UNSUPPORTED, "rt_set_scene: render kernel does not fit on an SM with %zu B shared memory", smem);
-    c->render_blocks_per_sm = bps;
+    // opt in to large dynamic shared memory; pick the CTA size that keeps the most warps resident per SM (one scene copy per
+    // CTA, so big scenes want big CTAs) and size the persistent grid to exactly fill the machine
+    const int optin = static_cast<int>(c->prop.sharedMemPerBlockOptin);
+    RT_CUDA(cudaFuncSetAttribute(rt::rt_render_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
+    RT_CUDA(cudaFuncSetAttribute(rt::rt_render_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
+    RT_CUDA(cudaFuncSetAttribute(rt::rt_primary_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
+    RT_CUDA(cudaFuncSetAttribute(rt::rt_primary_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
+    int best_tpb = 0, best_bps = 0;
+    for (int tpb = 256; tpb <= RT_MAX_TPB; tpb += 256) {
+        const size_t smem = cta_smem_bytes(n_pad, tpb);
+        if (smem > static_cast<size_t>(optin)) break;
+        int bps = 0;
+        RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, rt::rt_render_kernel<false>, tpb, smem));
+        if (bps * tpb > best_bps * best_tpb) { best_tpb = tpb; best_bps = bps; }
+    }
+    if (best_bps < 1) return fail(RT_ERR_UNSUPPORTED, "rt_set_scene: render kernel does not fit on an SM with %zu B shared memory", cta_smem_bytes(n_pad, 256));
+    c->tpb = best_tpb;
+    c->render_blocks_per_sm = best_bps;
     return RT_OK;
 }
 
@@ -508,11 +518,11 @@ int rt_render(rt_context* c, uint64_t first_sample, int spp, int max_depth, uint
         p.partial = c->partial;
     }
     RT_CUDA(cudaMemsetAsync(c->counters, 0, sizeof(u64), c->stream));
-    const size_t smem = scene_smem_bytes(c->n_pad);
+    const size_t smem = cta_smem_bytes(c->n_pad, c->tpb);
     const int grid = c->prop.multiProcessorCount * c->render_blocks_per_sm;
     EventPair ev = ev_begin(c, 0);
-    if (flags & RT_FLAG_DEBUG_NO_CULL_) rt::rt_render_kernel<true><<<grid, 256, smem, c->stream>>>(p);
-    else rt::rt_render_kernel<false><<<grid, 256, smem, c->stream>>>(p);
+    if (flags & RT_FLAG_DEBUG_NO_CULL_) rt::rt_render_kernel<true><<<grid, c->tpb, smem, c->stream>>>(p);
+    else rt::rt_render_kernel<false><<<grid, c->tpb, smem, c->stream>>>(p);
     ++c->launches;
     if (p.n_chunks > 1) {
         rt::rt_combine_kernel<<<static_cast<unsigned>((n_pix + 255) / 256), 256, 0, c->stream>>>(p.hdr, p.partial, p.n_chunks, n_pix);
@@ -569,10 +579,10 @@ int rt_primary_hits(rt_context* c, uint64_t sample, uint32_t flags, int32_t* sph
     rt::RenderParams p;
     if (int r = prepare_frames(c, sample, 1, 0, flags, p)) return r;
     p.chunk_spp = 1; p.n_chunks = 1;
-    const size_t smem = scene_smem_bytes(c->n_pad);
+    const size_t smem = cta_smem_bytes(c->n_pad, c->tpb);
     const int grid = c->prop.multiProcessorCount * std::max(1, c->render_blocks_per_sm);
-    if (flags & RT_FLAG_DEBUG_NO_CULL_) rt::rt_primary_kernel<true><<<grid, 256, smem, c->stream>>>(p, c->ids, c->mids);
-    else rt::rt_primary_kernel<false><<<grid, 256, smem, c->stream>>>(p, c->ids, c->mids);
+    if (flags & RT_FLAG_DEBUG_NO_CULL_) rt::rt_primary_kernel<true><<<grid, c->tpb, smem, c->stream>>>(p, c->ids, c->mids);
+    else rt::rt_primary_kernel<false><<<grid, c->tpb, smem, c->stream>>>(p, c->ids, c->mids);
     ++c->launches;
     RT_CUDA(cudaGetLastError());
     if (sphere_idx) RT_CUDA(cudaMemcpyAsync(sphere_idx, c->ids, n * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));

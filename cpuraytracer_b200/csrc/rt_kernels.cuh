@@ -41,12 +41,16 @@ struct RenderParams {
 
 enum LaneState { ST_NEED_ITEM = 0, ST_NEW_PATH = 1, ST_IN_PATH = 2, ST_DONE = 3 };
 
-__device__ __forceinline__ void stage_scene(const RenderParams& p, float4*& sA, float4*& sB, float2*& sC, float*& sR, unsigned char* smem) {
+// Shared-memory layout of one CTA: [cullA np*16][cullB np*16][cullC np*8][radius 2np*4][candidate lists 2*CAP*blockDim*4].
+// `lists` is this thread's column of the word-interleaved candidate lists (entry e at lists[e * blockDim.x]).
+#define RT_MAX_TPB 768
+__device__ __forceinline__ void stage_scene(const RenderParams& p, float4*& sA, float4*& sB, float2*& sC, float*& sR, uint32_t*& lists, unsigned char* smem) {
     const int np = p.n_pairs_pad;
     sA = reinterpret_cast<float4*>(smem);
     sB = sA + np;
     sC = reinterpret_cast<float2*>(sB + np);
     sR = reinterpret_cast<float*>(sC + np);
+    lists = reinterpret_cast<uint32_t*>(sR + 2 * np) + threadIdx.x;
     for (int i = threadIdx.x; i < np; i += blockDim.x) { sA[i] = p.cullA[i]; sB[i] = p.cullB[i]; sC[i] = p.cullC[i]; }
     for (int i = threadIdx.x; i < 2 * np; i += blockDim.x) sR[i] = p.radius[i];
     __syncthreads();
@@ -126,10 +130,11 @@ __device__ __forceinline__ bool item_to_pixel(const RenderParams& p, u64 item, i
 }
 
 template <bool NO_CULL>
-__global__ void __launch_bounds__(256) rt_render_kernel(const RenderParams p) {
+__global__ void __launch_bounds__(RT_MAX_TPB) rt_render_kernel(const RenderParams p) {
     extern __shared__ __align__(16) unsigned char smem[];
-    float4 *sA, *sB; float2* sC; float* sR;
-    stage_scene(p, sA, sB, sC, sR, smem);
+    float4 *sA, *sB; float2* sC; float* sR; uint32_t* lists;
+    stage_scene(p, sA, sB, sC, sR, lists, smem);
+    const int lstride = static_cast<int>(blockDim.x);
 
     const unsigned FULL = 0xffffffffu;
     const unsigned lane = threadIdx.x & 31u;
@@ -183,7 +188,7 @@ __global__ void __launch_bounds__(256) rt_render_kernel(const RenderParams p) {
         const bool active = (st == ST_IN_PATH);
 
         // ---- K2+K3: fused closest-hit / shadow query over every sphere ----
-        const QueryResult q = fused_query<NO_CULL>(sA, sB, sC, sR, p.n_groups, p.n_spheres, o, d, Ldir, active && want_closest, active && want_shadow);
+        const QueryResult q = fused_query<NO_CULL>(sA, sB, sC, sR, lists, lstride, p.n_groups, p.n_spheres, o, d, Ldir, active && want_closest, active && want_shadow);
         ++n_pass;
 
         // ---- K4: integrate ----
@@ -278,10 +283,10 @@ __global__ void rt_resolve_kernel(const float4* __restrict__ hdr, uint32_t* __re
 
 // K6: primary-hit id buffers (jitter/lens per flags) for frame `first_sample`.
 template <bool NO_CULL>
-__global__ void __launch_bounds__(256) rt_primary_kernel(const RenderParams p, int32_t* __restrict__ sphere_idx, int32_t* __restrict__ material_id) {
+__global__ void __launch_bounds__(RT_MAX_TPB) rt_primary_kernel(const RenderParams p, int32_t* __restrict__ sphere_idx, int32_t* __restrict__ material_id) {
     extern __shared__ __align__(16) unsigned char smem[];
-    float4 *sA, *sB; float2* sC; float* sR;
-    stage_scene(p, sA, sB, sC, sR, smem);
+    float4 *sA, *sB; float2* sC; float* sR; uint32_t* lists;
+    stage_scene(p, sA, sB, sC, sR, lists, smem);
     const u64 n_items = static_cast<u64>(p.tiles_x) * p.tiles_y * 32ull;
     for (u64 item = blockIdx.x * static_cast<u64>(blockDim.x) + threadIdx.x; item < ((n_items + 31ull) & ~31ull); item += static_cast<u64>(gridDim.x) * blockDim.x) {
         int chunk, px, py;
@@ -295,7 +300,7 @@ __global__ void __launch_bounds__(256) rt_primary_kernel(const RenderParams p, i
             const float v = (static_cast<float>(py) + jy) / static_cast<float>(p.H);
             camera_get_ray(p.cam, u, v, lx, ly, o, d);
         }
-        const QueryResult q = fused_query<NO_CULL>(sA, sB, sC, sR, p.n_groups, p.n_spheres, o, d, mk3(p.Lx, p.Ly, p.Lz), valid, false);
+        const QueryResult q = fused_query<NO_CULL>(sA, sB, sC, sR, lists, static_cast<int>(blockDim.x), p.n_groups, p.n_spheres, o, d, mk3(p.Lx, p.Ly, p.Lz), valid, false);
         if (valid) {
             const int pix = py * p.W + px;
             if (sphere_idx) sphere_idx[pix] = q.idx;
