@@ -11,7 +11,8 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "csrc", "librt_b200.so")
+# RT_B200_LIB: developer override used by tools/variants.py to A/B experimental builds of the same source
+LIB_PATH = os.environ.get("RT_B200_LIB") or os.path.join(HERE, "csrc", "librt_b200.so")
 
 RT_OK = 0
 STATUS_NAMES = {0: "RT_OK", 1: "RT_ERR_INVALID_ARGUMENT", 2: "RT_ERR_CUDA", 3: "RT_ERR_OUT_OF_MEMORY",

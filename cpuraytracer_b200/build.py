@@ -40,10 +40,11 @@ def needs_build() -> bool:
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
-    if not force and not needs_build():
+def build(force: bool = False, verbose: bool = False, out: str | None = None, extra: list[str] | None = None) -> str:
+    """`out` / `extra` build an experimental variant (tools/variants.py) beside the product library."""
+    if out is None and not force and not needs_build():
         return LIB
-    cmd = [_nvcc(), *NVCC_FLAGS, "-o", LIB, os.path.join(CSRC, "rt_b200.cu")]
+    cmd = [_nvcc(), *NVCC_FLAGS, *(extra or []), "-o", out or LIB, os.path.join(CSRC, "rt_b200.cu")]
     if verbose:
         cmd.insert(1, "-Xptxas=-v")
         print(" ".join(cmd), file=sys.stderr)
@@ -52,7 +53,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
         raise RuntimeError("nvcc failed:\n" + r.stdout + r.stderr)
     if verbose:
         print(r.stdout + r.stderr, file=sys.stderr)
-    return LIB
+    return out or LIB
 
 
 if __name__ == "__main__":
