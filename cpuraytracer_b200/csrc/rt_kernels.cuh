@@ -46,8 +46,10 @@ enum LaneState { ST_NEED_ITEM = 0, ST_NEW_PATH = 1, ST_IN_PATH = 2, ST_DONE = 3 
 #ifndef RT_MAX_TPB
 #define RT_MAX_TPB 768
 #endif
-#ifndef RT_MIN_BLOCKS
-#define RT_MIN_BLOCKS 1
+#ifdef RT_MIN_BLOCKS
+#define RT_RENDER_BOUNDS __launch_bounds__(RT_MAX_TPB, RT_MIN_BLOCKS)
+#else
+#define RT_RENDER_BOUNDS __launch_bounds__(RT_MAX_TPB)
 #endif
 __device__ __forceinline__ void stage_scene(const RenderParams& p, float4*& sA, float4*& sB, float2*& sC, float*& sR, uint32_t*& lists, unsigned char* smem) {
     const int np = p.n_pairs_pad;
@@ -135,7 +137,7 @@ __device__ __forceinline__ bool item_to_pixel(const RenderParams& p, u64 item, i
 }
 
 template <bool NO_CULL>
-__global__ void __launch_bounds__(RT_MAX_TPB, RT_MIN_BLOCKS) rt_render_kernel(const RenderParams p) {
+__global__ void RT_RENDER_BOUNDS rt_render_kernel(const RenderParams p) {
     extern __shared__ __align__(16) unsigned char smem[];
     float4 *sA, *sB; float2* sC; float* sR; uint32_t* lists;
     stage_scene(p, sA, sB, sC, sR, lists, smem);
