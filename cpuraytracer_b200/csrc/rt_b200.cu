@@ -161,7 +161,7 @@ int rt_scene_add_directional_light(rt_scene* s, const float dir[3], const float 
     const host::V3 n = host::normalize3({dir[0], dir[1], dir[2]});           // light.cpp:7
     if (!(host::dot3(n, n) > 0.f)) return fail(RT_ERR_INVALID_ARGUMENT, "rt_scene_add_directional_light: zero direction");
     rt_light_desc l{};
-    l.dir[0] = n.x; l.dir[1] = n.y; l.dir[2] = n.z;
+    l.dir[0] = dir[0]; l.dir[1] = dir[1]; l.dir[2] = dir[2];          // the ctor argument; normalised when bound (rt_set_scene)
     for (int k = 0; k < 4; ++k) l.color[k] = host::xmcolor_roundtrip(rgba[k]);   // light.cpp:8
     l.luminance = luminance;
     s->lights.push_back(l);
@@ -343,8 +343,9 @@ int rt_set_scene(rt_context* c, const rt_scene* s) {
     if (cta_smem_bytes(n_pad, 256) > static_cast<size_t>(c->prop.sharedMemPerBlockOptin))
         return fail(RT_ERR_UNSUPPORTED, "rt_set_scene: %d spheres need %zu B of shared memory per CTA, device limit is %zu", n, cta_smem_bytes(n_pad, 256), static_cast<size_t>(c->prop.sharedMemPerBlockOptin));
     const bool has_light = !s->lights.empty();
-    double L[3] = {0, 0, 0};
-    if (has_light) for (int k = 0; k < 3; ++k) L[k] = s->lights[0].dir[k];
+    host::V3 Ln{0.f, 0.f, 0.f};
+    if (has_light) Ln = host::normalize3({s->lights[0].dir[0], s->lights[0].dir[1], s->lights[0].dir[2]});   // light.cpp:7
+    const double L[3] = {Ln.x, Ln.y, Ln.z};
     std::vector<float4> A(np), B(np); std::vector<float2> C(np); std::vector<float> R(n_pad, 0.f);
     std::vector<rt::DevMat> M(std::max(n, 1));
     const double K = static_cast<double>(RT_CULL_K);
@@ -393,7 +394,7 @@ int rt_set_scene(rt_context* c, const rt_scene* s) {
     b.Lx = b.Ly = b.Lz = 0.f; b.lcx = b.lcy = b.lcz = 0.f;
     if (has_light) {
         const rt_light_desc& l = s->lights[0];
-        b.Lx = l.dir[0]; b.Ly = l.dir[1]; b.Lz = l.dir[2];
+        b.Lx = Ln.x; b.Ly = Ln.y; b.Lz = Ln.z;
         b.lcx = l.luminance * l.color[0]; b.lcy = l.luminance * l.color[1]; b.lcz = l.luminance * l.color[2];   // light.cpp:27
     }
     const rt_texture_desc& sky = s->textures[s->sky_texture];              // Emissive::Emit at uv = (0,0): material.cpp:172-175

@@ -41,7 +41,7 @@ typedef enum rt_status {
 typedef struct rt_sphere_desc   { float cx, cy, cz, radius; int32_t material; } rt_sphere_desc;            /* ray-tracing.h:53-58 */
 typedef struct rt_material_desc { int32_t kind; int32_t texture; float smoothness; float ior; } rt_material_desc; /* material.h */
 typedef struct rt_texture_desc  { int32_t kind; float tiling; float c0[4]; float c1[4]; } rt_texture_desc;    /* texture.h */
-typedef struct rt_light_desc    { float dir[3]; float color[4]; float luminance; } rt_light_desc;            /* light.h:15-21, dir normalised */
+typedef struct rt_light_desc    { float dir[3]; float color[4]; float luminance; } rt_light_desc;            /* light.h:15-21; dir as given to the ctor (consumers normalise it, light.cpp:7) */
 
 /* material ids (also the values written to the primary-hit material buffer) */
 enum { RT_MAT_OPAQUE = 0,        /* DielectricOpaque,       material.h:37-52 */

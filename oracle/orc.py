@@ -23,6 +23,7 @@ FLAG_JITTER_OFF, FLAG_LENS_OFF = 1, 2
 RNG_COUNTER, RNG_HALTON = 0, 1
 ACCEL_BRUTE, ACCEL_BVH = 0, 1
 INTEGRATOR_ITERATIVE, INTEGRATOR_RECURSIVE = 0, 1
+MATH_PINNED, MATH_REFERENCE = 0, 1
 MAT_OPAQUE, MAT_METAL, MAT_TRANSPARENT, MAT_SKY = 0, 1, 2, 3
 
 
@@ -47,7 +48,7 @@ class OrcCamera(C.Structure):
 class OrcConfig(C.Structure):
     _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("first_sample", C.c_uint64), ("spp", C.c_int32),
                 ("max_depth", C.c_int32), ("flags", C.c_uint32), ("rng_mode", C.c_int32), ("accel", C.c_int32),
-                ("integrator", C.c_int32), ("threads", C.c_int32), ("exposure_stops", C.c_float), ("seed", C.c_uint32)]
+                ("integrator", C.c_int32), ("threads", C.c_int32), ("exposure_stops", C.c_float), ("seed", C.c_uint32), ("math_mode", C.c_int32)]
 
 
 class OrcStats(C.Structure):
@@ -83,6 +84,8 @@ def load() -> C.CDLL:
     lib.orc_primary_hits.argtypes = [C.POINTER(OrcScene), C.POINTER(OrcCameraParams), C.POINTER(OrcConfig), P, P]
     lib.orc_resolve_ldr.restype = None
     lib.orc_resolve_ldr.argtypes = [P, C.c_int64, C.c_uint64, P]
+    lib.orc_set_math_mode.restype = None
+    lib.orc_set_math_mode.argtypes = [C.c_int]
     lib.orc_halton.restype = F
     lib.orc_halton.argtypes = [C.c_uint64, C.c_uint32]
     lib.orc_halton_disk.restype = None
@@ -154,9 +157,9 @@ def camera_params(origin, look_at, vfov_deg, aspect, focus, aperture) -> OrcCame
 
 
 def config(width, height, spp=1, max_depth=50, first_sample=1, flags=0, rng_mode=RNG_COUNTER, accel=ACCEL_BRUTE,
-           integrator=INTEGRATOR_ITERATIVE, threads=0, exposure_stops=-15.0, seed=0) -> OrcConfig:
+           integrator=INTEGRATOR_ITERATIVE, threads=0, exposure_stops=-15.0, seed=0, math_mode=0) -> OrcConfig:
     return OrcConfig(width, height, first_sample, spp, max_depth, flags, rng_mode, accel, integrator, threads,
-                     exposure_stops, seed)
+                     exposure_stops, seed, math_mode)
 
 
 def render(scene: Scene, cam: OrcCameraParams, cfg: OrcConfig, hdr: np.ndarray | None = None):
@@ -186,3 +189,86 @@ def resolve_ldr(hdr: np.ndarray, sample_count: int) -> np.ndarray:
     out = np.empty((h, w), np.uint32)
     load().orc_resolve_ldr(hdr.ctypes.data, h * w, sample_count, out.ctypes.data)
     return out
+
+
+# ------------------------------------------------------------------------------------------------ tier A: oracle/_ref
+REF_LIB_PATH = os.path.join(HERE, "_ref", "libref.so")
+_ref = None
+
+
+def load_ref():
+    """oracle/_ref/libref.so = the reference's own common-lib .cpp files compiled against dxm_shim/ + ref_driver.cpp.
+    Built by `make -C oracle` where /root/reference exists; travels to the GPU box as a prebuilt file.  None if absent."""
+    global _ref
+    if _ref is not None:
+        return _ref
+    if not os.path.exists(REF_LIB_PATH):
+        if os.path.isdir("/root/reference/src/common-lib"):
+            subprocess.run(["make", "-C", HERE, "ref"], capture_output=True, text=True)
+        if not os.path.exists(REF_LIB_PATH):
+            return None
+    lib = C.CDLL(REF_LIB_PATH)
+    F, P = C.c_float, C.c_void_p
+    FP = C.POINTER(C.c_float)
+    lib.ref_render.restype = C.c_int
+    lib.ref_render.argtypes = [C.POINTER(OrcScene), C.POINTER(OrcCameraParams), C.POINTER(OrcConfig), P, C.POINTER(OrcStats)]
+    lib.ref_primary_hits.restype = C.c_int
+    lib.ref_primary_hits.argtypes = [C.POINTER(OrcScene), C.POINTER(OrcCameraParams), C.POINTER(OrcConfig), P, P]
+    lib.ref_resolve_ldr.restype = None
+    lib.ref_resolve_ldr.argtypes = [P, C.c_int64, C.c_uint64, P]
+    lib.ref_halton.restype = F
+    lib.ref_halton.argtypes = [C.c_uint64, C.c_uint32]
+    lib.ref_halton_disk.restype = None
+    lib.ref_halton_disk.argtypes = [C.c_uint64, C.c_uint32, C.c_uint32, FP]
+    lib.ref_halton_hemisphere.restype = None
+    lib.ref_halton_hemisphere.argtypes = [C.c_uint64, C.c_uint32, C.c_uint32, FP]
+    lib.ref_camera_get_ray.restype = None
+    lib.ref_camera_get_ray.argtypes = [C.POINTER(OrcCameraParams), F, F, F, F, FP, FP]
+    lib.ref_sphere_intersect.restype = C.c_int
+    lib.ref_sphere_intersect.argtypes = [P, FP, FP, FP, FP, FP, FP]
+    lib.ref_closest_hit.restype = C.c_int
+    lib.ref_closest_hit.argtypes = [C.POINTER(OrcScene), FP, FP, FP]
+    lib.ref_texture_eval.restype = None
+    lib.ref_texture_eval.argtypes = [P, F, F, FP]
+    lib.ref_fresnel_term.restype = F
+    lib.ref_fresnel_term.argtypes = [F, F]
+    lib.ref_reflect.restype = None
+    lib.ref_reflect.argtypes = [FP, FP, FP]
+    lib.ref_refract.restype = None
+    lib.ref_refract.argtypes = [FP, FP, F, FP]
+    lib.ref_xmcolor_quantize.restype = C.c_uint8
+    lib.ref_xmcolor_quantize.argtypes = [F]
+    lib.ref_xmcolor_load.restype = F
+    lib.ref_xmcolor_load.argtypes = [C.c_uint8]
+    lib.ref_scatter_sequence.restype = C.c_int
+    lib.ref_scatter_sequence.argtypes = [C.POINTER(OrcScene), C.c_int, C.c_int, P, P, P, P, P, P]
+    lib.ref_shade_hit.restype = C.c_int
+    lib.ref_shade_hit.argtypes = [C.POINTER(OrcScene), FP, FP, FP, FP]
+    lib.ref_build_info.restype = C.c_char_p
+    lib.ref_build_info.argtypes = []
+    _ref = lib
+    return lib
+
+
+def ref_render(scene: Scene, cam: OrcCameraParams, cfg: OrcConfig, hdr: np.ndarray | None = None):
+    """The reference's own classes (atomic Halton counters + BVH + recursion).  Returns (hdr sum, OrcStats)."""
+    lib = load_ref()
+    if lib is None:
+        raise RuntimeError("oracle/_ref/libref.so is not built (needs /root/reference)")
+    if hdr is None:
+        hdr = np.zeros((cfg.height, cfg.width, 4), np.float32)
+    st = OrcStats()
+    rc = lib.ref_render(C.byref(scene.c), C.byref(cam), C.byref(cfg), hdr.ctypes.data, C.byref(st))
+    if rc != 0:
+        raise ValueError(f"ref_render: bad argument ({rc})")
+    return hdr, st
+
+
+def ref_primary_hits(scene: Scene, cam: OrcCameraParams, cfg: OrcConfig):
+    lib = load_ref()
+    ids = np.empty((cfg.height, cfg.width), np.int32)
+    mids = np.empty((cfg.height, cfg.width), np.int32)
+    rc = lib.ref_primary_hits(C.byref(scene.c), C.byref(cam), C.byref(cfg), ids.ctypes.data, mids.ctypes.data)
+    if rc != 0:
+        raise ValueError(f"ref_primary_hits: bad argument ({rc})")
+    return ids, mids

@@ -33,6 +33,9 @@
 #include <memory>
 #include <thread>
 #include <vector>
+#if defined(__SSE__)
+#include <xmmintrin.h>
+#endif
 
 namespace {
 
@@ -108,13 +111,27 @@ static inline float fresnel_term(float c, float ior) {
     res = res * gac;
     return std::fmin(std::fmax(res, 0.0f), 1.0f);
 }
-static inline float pow5(float x) { const float x2 = x * x; return (x2 * x2) * x; }          /* D1 */
+/* Math mode (test-only global, constant during a render): 0 = pinned (D1-D3 below hold, CPU == GPU bit for bit),
+ * 1 = reference libm: powf(x,5), libm cosf/sinf and rcpps exactly as the reference binary calls them, so that this
+ * restatement can be compared bit for bit with oracle/_ref (the reference's own sources). */
+static int g_math_ref = 0;
+static inline float pow5(float x) {                                                            /* D1 */
+    if (g_math_ref) return std::pow(x, 5.f);                                                   /* XMVectorPow = powf per lane */
+    const float x2 = x * x; return (x2 * x2) * x;
+}
+static inline float rcp_ior(float ior) {                                                       /* D3 */
+#if defined(__SSE__)
+    if (g_math_ref) return _mm_cvtss_f32(_mm_rcp_ss(_mm_set_ss(ior)));                         /* XMVectorReciprocalEst = rcpps */
+#endif
+    return 1.0f / ior;
+}
 /* f0 + (1 - f0) * (1 - nDotV)^5, material.cpp:27 / light.cpp:37. */
 static inline float schlick(float f0, float n_dot_v) { return f0 + (1.0f - f0) * pow5(1.0f - n_dot_v); }
 
 /* D2: pinned sin/cos for theta in [0, 2*pi].  Two-constant Cody-Waite reduction by pi/2 with
  * explicit fused multiply-adds, cephes minimax polynomials on [-pi/4, pi/4], Horner with fmaf. */
 static inline void sincos_pinned(float theta, float* s_out, float* c_out) {
+    if (g_math_ref) { *s_out = std::sin(theta); *c_out = std::cos(theta); return; }              /* quasi-random.cpp:46-47,58-59 */
     const float q = std::nearbyint(theta * 0.63661975f);          /* 2/pi, round-to-nearest-even */
     float r = std::fmaf(-q, 1.57079637050628662109375f, theta);    /* pi/2 high part */
     r = std::fmaf(-q, -4.37113900018624283e-8f, r);                /* pi/2 low part  */
@@ -337,6 +354,7 @@ struct World {
     int accel, rng_mode, integrator, max_depth;
     uint32_t seed;
     std::unique_ptr<Counters[]> counters;       /* per material instance, material.h:34,50-51,67 */
+    std::vector<V3> light_dir;                  /* DirectionalLight::m_direction = XMVector3Normalize(dir), light.cpp:7 */
     V3 sky;
     std::atomic<uint64_t> closest_rays{0}, shadow_rays{0};
 };
@@ -367,7 +385,7 @@ static inline V3 shade(const World& w, const Hit& h, V3 view_origin, RayCount& r
     V3 total{0.f, 0.f, 0.f};
     for (int li = 0; li < w.sc->n_lights; ++li) {
         const orc_light& lt = w.sc->lights[li];
-        const V3 L = v3(lt.dir);
+        const V3 L = w.light_dir[li];                                     /* m_direction, normalised at light.cpp:7 */
         Hit dummy;
         ++rc.shadow;
         if (closest_hit(w, Ray{h.pos, L}, dummy)) continue;               /* light.cpp:13-18 (adds zero) */
@@ -428,7 +446,7 @@ static inline bool scatter_with(const World& w, const Ray& r, const Hit& h, cons
     V3 outward; float eta, cos_i;
     const float dn = dot3(r.d, h.n);
     if (dn > 0.f) { outward = neg(h.n); eta = m.ior; cos_i = dn; }        /* :121-127 */
-    else { outward = h.n; eta = 1.0f / m.ior; cos_i = dot3(r.d, neg(h.n)); }   /* :128-134, D3 */
+    else { outward = h.n; eta = rcp_ior(m.ior); cos_i = dot3(r.d, neg(h.n)); }   /* :128-134, D3 */
     const V3 refr = refract3(r.d, outward, eta);                          /* :137 */
     const bool can_refract = (refr.x != 0.f) || (refr.y != 0.f) || (refr.z != 0.f);   /* :138 */
     const float prob = can_refract ? fresnel_term(cos_i, m.ior) : 1.0f;   /* :140-149 */
@@ -503,8 +521,13 @@ static V3 hit_color_iterative(World& w, Ray r, uint32_t pixel, uint64_t sample, 
     return L;
 }
 
+static void world_lights(World& w) {
+    w.light_dir.clear();
+    for (int i = 0; i < w.sc->n_lights; ++i) w.light_dir.push_back(normalize3(v3(w.sc->lights[i].dir)));
+}
 static void world_init(World& w, const orc_scene* sc, const orc_camera_params* cp, const orc_config* cfg) {
     w.sc = sc;
+    world_lights(w);
     camera_make(cp, &w.cam);
     w.accel = cfg->accel; w.rng_mode = cfg->rng_mode; w.integrator = cfg->integrator;
     w.max_depth = cfg->max_depth; w.seed = cfg->seed;
@@ -544,6 +567,7 @@ extern "C" {
 
 int orc_render(const orc_scene* sc, const orc_camera_params* cp, const orc_config* cfg, float* hdr, orc_stats* stats) {
     if (!sc || !cp || !cfg || !hdr || cfg->width <= 0 || cfg->height <= 0 || cfg->spp < 0 || cfg->first_sample < 1) return 1;
+    g_math_ref = cfg->math_mode;
     World w; world_init(w, sc, cp, cfg);
     int threads = cfg->threads > 0 ? cfg->threads : static_cast<int>(std::thread::hardware_concurrency());
     if (threads < 1) threads = 1;
@@ -579,6 +603,7 @@ int orc_render(const orc_scene* sc, const orc_camera_params* cp, const orc_confi
 
 int orc_primary_hits(const orc_scene* sc, const orc_camera_params* cp, const orc_config* cfg, int32_t* sphere_idx, int32_t* material_id) {
     if (!sc || !cp || !cfg || cfg->width <= 0 || cfg->height <= 0 || cfg->first_sample < 1) return 1;
+    g_math_ref = cfg->math_mode;
     World w; world_init(w, sc, cp, cfg);
     int threads = cfg->threads > 0 ? cfg->threads : static_cast<int>(std::thread::hardware_concurrency());
     const uint64_t n = cfg->first_sample;
@@ -613,6 +638,7 @@ void orc_resolve_ldr(const float* hdr, int64_t n_pixels, uint64_t sample_count, 
     }
 }
 
+void orc_set_math_mode(int mode) { g_math_ref = mode; }
 float orc_halton(uint64_t index, uint32_t base) { return halton(index, base); }
 void orc_halton_disk(uint64_t index, uint32_t b1, uint32_t b2, float out[2]) { disk_from_u(halton(index, b1), halton(index, b2), &out[0], &out[1]); }
 void orc_halton_hemisphere(uint64_t index, uint32_t b1, uint32_t b2, float out[3]) { st3(out, hemisphere_from_u(halton(index, b1), halton(index, b2))); }
@@ -661,6 +687,7 @@ int orc_scatter(const orc_scene* sc, int sphere, const float o[3], const float d
 }
 int orc_shade_hit(const orc_scene* sc, const float view_origin[3], const float o[3], const float d[3], int accel, float rgb[3]) {
     World w; w.sc = sc; w.accel = accel;
+    world_lights(w);
     if (accel == ORC_ACCEL_BVH) w.bvh.make(sc);
     Hit h;
     if (!closest_hit(w, Ray{v3(o), v3(d)}, h)) return -1;

@@ -7,14 +7,16 @@
  * load this library.  The product (cpuraytracer_b200/, include/rt_b200.h) never links, imports
  * or calls anything in this directory.
  *
- * PARITY PIN STATUS: the reference ships no tests or golden vectors, and its
- * arithmetic lives in DirectXMath (Windows SDK 10.0.16299.0, not vendored).  This restatement is
- * pinned two ways: (1) tests/test_oracle_kat.py holds the known-answer tests SURVEY.md 8(c)
- * derives from the reference source, and (2) oracle/_ref (see oracle/Makefile) compiles the
- * reference's own camera/light/material/quasi-random/ray-tracing/texture .cpp files, unmodified
- * and in place, against a from-scratch DirectXMath shim, and tests/test_oracle_vs_ref.py checks
- * this restatement against that build function by function.  The DirectXMath shim itself is
- * restated from memory of the SSE2 code paths => "parity unpinned at the DirectXMath boundary".
+ * PARITY PIN STATUS: the reference ships no tests or golden vectors, and its arithmetic lives in
+ * DirectXMath (Windows SDK 10.0.16299.0, not vendored).  This restatement is pinned three ways:
+ *   (1) tests/test_oracle_kat.py: known-answer tests derived by hand from the cited reference lines;
+ *   (2) tests/test_oracle_vs_ref.py: oracle/_ref (oracle/Makefile) compiles the reference's OWN camera / light / material /
+ *       quasi-random / ray-tracing / texture .cpp files, unmodified and in place, against a from-scratch DirectXMath
+ *       stand-in (dxm_shim/); in ORC_MATH_REFERENCE mode this restatement agrees with that build BIT FOR BIT, function by
+ *       function and for whole depth-50 renders of the default scene;
+ *   (3) tests/golden/*.npz: outputs of that reference build, committed with the script that made them.
+ * What remains unpinned is the DirectXMath stand-in itself (restated from memory of the SSE2 code paths):
+ * "parity unpinned at the DirectXMath boundary".
  */
 #ifndef RT_ORACLE_H
 #define RT_ORACLE_H
@@ -27,7 +29,7 @@ extern "C" {
 typedef struct orc_sphere   { float cx, cy, cz, radius; int32_t material; } orc_sphere;          /* 20 B */
 typedef struct orc_material { int32_t kind; int32_t texture; float smoothness; float ior; } orc_material; /* 16 B */
 typedef struct orc_texture  { int32_t kind; float tiling; float c0[4]; float c1[4]; } orc_texture; /* 40 B */
-typedef struct orc_light    { float dir[3]; float color[4]; float luminance; } orc_light;        /* 32 B, dir normalised */
+typedef struct orc_light    { float dir[3]; float color[4]; float luminance; } orc_light;        /* 32 B; dir as passed to the DirectionalLight ctor (normalised by the consumer, light.cpp:7) */
 
 enum { ORC_MAT_OPAQUE = 0, ORC_MAT_METAL = 1, ORC_MAT_TRANSPARENT = 2, ORC_MAT_SKY = 3 };
 enum { ORC_TEX_CONST = 0, ORC_TEX_CHECKER = 1 };
@@ -50,6 +52,9 @@ enum { ORC_FLAG_JITTER_OFF = 1u, ORC_FLAG_LENS_OFF = 2u };
 enum { ORC_RNG_COUNTER = 0, ORC_RNG_HALTON = 1 };     /* HALTON = the reference's per-material atomic counters */
 enum { ORC_ACCEL_BRUTE = 0, ORC_ACCEL_BVH = 1 };      /* BVH = the reference's BvhNode restated */
 enum { ORC_INTEGRATOR_ITERATIVE = 0, ORC_INTEGRATOR_RECURSIVE = 1 };
+/* PINNED: pow5 by multiplication, pinned sincos, exact 1/ior (CPU == GPU bit for bit).  REFERENCE: powf, libm sinf/cosf and
+ * rcpps as the reference binary calls them (comparable bit for bit with oracle/_ref; x86 only). */
+enum { ORC_MATH_PINNED = 0, ORC_MATH_REFERENCE = 1 };
 
 typedef struct orc_config {
     int32_t  width, height;
@@ -61,6 +66,7 @@ typedef struct orc_config {
     int32_t  threads;           /* 0 = hardware_concurrency */
     float    exposure_stops;    /* m_exposure, spheres-app.cpp:48 (-15) */
     uint32_t seed;              /* counter RNG only */
+    int32_t  math_mode;         /* ORC_MATH_PINNED (default) or ORC_MATH_REFERENCE */
 } orc_config;
 
 typedef struct orc_stats { uint64_t paths, closest_rays, shadow_rays; double seconds; } orc_stats;
@@ -72,6 +78,7 @@ int  orc_primary_hits(const orc_scene*, const orc_camera_params*, const orc_conf
 void orc_resolve_ldr(const float* hdr_rgba, int64_t n_pixels, uint64_t sample_count, uint32_t* bgra8);
 
 /* ---- unit-level entry points for known-answer tests ---- */
+void     orc_set_math_mode(int mode);                                                  /* for the unit-level entry points below */
 float    orc_halton(uint64_t index, uint32_t base);                                   /* quasi-random.cpp:3-16 */
 void     orc_halton_disk(uint64_t index, uint32_t b1, uint32_t b2, float out[2]);      /* quasi-random.cpp:52-61 */
 void     orc_halton_hemisphere(uint64_t index, uint32_t b1, uint32_t b2, float out[3]);/* quasi-random.cpp:36-50 */

@@ -77,7 +77,7 @@ def test_scene_recorder_counts_and_ids(rt):
     frac = [np.mean(kinds == k) for k in (0, 1, 2)]
     assert 0.7 < frac[0] < 0.9 and 0.08 < frac[1] < 0.22 and 0.01 < frac[2] < 0.1     # 80 / 15 / 5 % recipe
     assert flat.sky_luminance == 8000.0 and flat.lights[0]["luminance"] == 40000.0
-    assert np.allclose(flat.lights[0]["dir"], 1 / np.sqrt(3))
+    assert list(flat.lights[0]["dir"]) == [1.0, 1.0, 1.0]      # the ctor argument; consumers normalise (light.cpp:7)
 
 
 def test_scene_is_reproducible_and_s4096(rt):

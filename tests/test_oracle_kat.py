@@ -232,8 +232,7 @@ def _one_sphere_scene(orc, kind, color=(0.5, 0.5, 0.5, 1.0), smoothness=16.0, li
     te[1] = (0, 0.0, (0.5, 0.5, 0.5, 1), (0.5, 0.5, 0.5, 1))
     li = np.zeros(1 if light else 0, orc.LIGHT_DTYPE)
     if light:
-        s = 1 / math.sqrt(3)
-        li[0] = ((s, s, s), (1, 1, 1, 1), 100.0)
+        li[0] = ((1, 1, 1), (1, 1, 1, 1), 100.0)
     return orc.Scene(sp, ma, te, li, 10.0, 1)
 
 
