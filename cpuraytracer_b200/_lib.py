@@ -61,6 +61,7 @@ SYMBOLS = [
     ("rt_context_destroy", None, [_P]),
     ("rt_last_error", C.c_char_p, []),
     ("rt_set_stream", C.c_int, [_P, _P]),
+    ("rt_get_stream", _P, [_P]),
     ("rt_synchronize", C.c_int, [_P]),
     ("rt_scene_create", C.c_int, [C.POINTER(_P)]),
     ("rt_scene_destroy", None, [_P]),

@@ -25,6 +25,41 @@ NVCC_FLAGS = [
 ]
 
 
+GROUP_LIB = os.path.join(CSRC, "librt_b200_group.so")
+APPS = os.path.normpath(os.path.join(HERE, "..", "apps"))
+CLI = os.path.join(APPS, "spheres")
+INCLUDE = os.path.normpath(os.path.join(HERE, "..", "include"))
+CUDA_HOME = os.environ.get("CUDA_HOME", "/usr/local/cuda")
+HOST_FLAGS = ["-std=c++17", "-O2", "-Wall", "-ffp-contract=off", "-fPIC", f"-I{CUDA_HOME}/include"]
+CUDART_STATIC = [f"-L{CUDA_HOME}/lib64", "-lcudart_static", "-ldl", "-lrt", "-lpthread"]
+
+
+def _stale(target: str, deps: list[str]) -> bool:
+    return not os.path.exists(target) or any(os.path.getmtime(d) > os.path.getmtime(target) for d in deps)
+
+
+def build_host(force: bool = False) -> tuple[str, str]:
+    """The C++17 host side above the C ABI: librt_b200_group.so (single-process multi-GPU sharding + ncclReduce,
+    include/rt_b200_group.h) and apps/spheres (headless replacement of the reference executable).  Host code only (g++)."""
+    cxx = os.environ.get("CXX") or shutil.which("g++") or "g++"
+    hdrs = [os.path.join(INCLUDE, h) for h in ("rt_b200.h", "rt_b200.hpp", "rt_b200_group.h", "rt_image_io.hpp")]
+    src = os.path.join(CSRC, "rt_group.cpp")
+    if force or _stale(GROUP_LIB, [src, LIB, *hdrs]):
+        cmd = [cxx, *HOST_FLAGS, "-fvisibility=hidden", "-shared", "-o", GROUP_LIB, src, f"-L{CSRC}", "-lrt_b200",
+               *CUDART_STATIC, "-Wl,-rpath,$ORIGIN"]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError("g++ (rt_group) failed:\n" + " ".join(cmd) + "\n" + r.stdout + r.stderr)
+    main = os.path.join(APPS, "spheres_main.cpp")
+    if force or _stale(CLI, [main, GROUP_LIB, LIB, *hdrs]):
+        cmd = [cxx, *HOST_FLAGS, "-o", CLI, main, f"-L{CSRC}", "-lrt_b200_group", "-lrt_b200",
+               "-Wl,-rpath,$ORIGIN/../cpuraytracer_b200/csrc"]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError("g++ (apps/spheres) failed:\n" + " ".join(cmd) + "\n" + r.stdout + r.stderr)
+    return GROUP_LIB, CLI
+
+
 def _nvcc() -> str:
     for cand in (os.environ.get("NVCC"), shutil.which("nvcc"), "/usr/local/cuda/bin/nvcc"):
         if cand and os.path.exists(cand):
@@ -58,3 +93,4 @@ def build(force: bool = False, verbose: bool = False, out: str | None = None, ex
 
 if __name__ == "__main__":
     print(build(force="--force" in sys.argv, verbose=True))
+    print(*build_host(force="--force" in sys.argv))

@@ -319,6 +319,7 @@ int rt_set_stream(rt_context* c, void* s) {
     c->stream = static_cast<cudaStream_t>(s);
     return RT_OK;
 }
+void* rt_get_stream(rt_context* c) { return c ? static_cast<void*>(c->stream) : nullptr; }
 int rt_synchronize(rt_context* c) {
     if (!c) return fail(RT_ERR_INVALID_ARGUMENT, "rt_synchronize: ctx is NULL");
     if (int r = ctx_use(c)) return r;

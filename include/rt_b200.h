@@ -83,6 +83,7 @@ RT_API int  rt_context_create(int device, rt_context** out);
 RT_API void rt_context_destroy(rt_context* ctx);
 RT_API const char* rt_last_error(void);                        /* thread-local message of the last failure */
 RT_API int  rt_set_stream(rt_context* ctx, void* cuda_stream); /* borrow a cudaStream_t (e.g. torch's current stream) */
+RT_API void* rt_get_stream(rt_context* ctx);                   /* the cudaStream_t the context launches on (e.g. to enqueue an ncclReduce behind the render) */
 RT_API int  rt_synchronize(rt_context* ctx);
 
 /* ---- scene recorder: mirrors the reference constructors ---- */
