@@ -31,6 +31,35 @@ def reduce_hdr(hdr_tensor, dst: int = 0, group=None):
     return hdr_tensor
 
 
+class ShardedAccumulator:
+    """The multi-call protocol of a sharded render, independent of who renders (CUDA library, or the oracle in the gloo
+    tests): rank 0's buffer is the job's running sum (m_backbufferHdr); before each call every other rank zeroes its
+    buffer so the reduce adds only this call's frames to rank 0."""
+
+    def __init__(self, hdr, render_into: Callable[[int, int], None], group=None):
+        import torch.distributed as dist
+        self.hdr, self.render_into, self.group = hdr, render_into, group
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.sample_count = 0
+
+    def clear(self) -> None:
+        self.hdr.zero_()
+        self.sample_count = 0
+
+    def render(self, spp: int, first_sample: Optional[int] = None, reduce: bool = True):
+        first = self.sample_count + 1 if first_sample is None else first_sample
+        my_first, my_spp = shard_samples(first, spp, self.rank, self.world)
+        if reduce and self.rank != 0 and self.world > 1:
+            self.hdr.zero_()
+        if my_spp > 0:
+            self.render_into(my_first, my_spp)
+        if reduce:
+            reduce_hdr(self.hdr, 0, self.group)
+        self.sample_count += spp
+        return self.hdr
+
+
 class ShardedRenderer:
     """One rank's share of a multi-GPU render.  The running-sum buffer is a torch CUDA tensor bound into the
     rt_context (rt_hdr_bind_external), so NCCL reduces the very buffer the kernel accumulated into; the kernels
@@ -38,11 +67,7 @@ class ShardedRenderer:
 
     def __init__(self, width: int, height: int, device: Optional[int] = None, group=None):
         import torch
-        import torch.distributed as dist
         from .api import Renderer
-        self.torch, self.dist, self.group = torch, dist, group
-        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
-        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.device = torch.cuda.current_device() if device is None else device
         with torch.cuda.device(self.device):
             self.hdr = torch.zeros((height, width, 4), dtype=torch.float32, device=f"cuda:{self.device}")
@@ -50,7 +75,13 @@ class ShardedRenderer:
         self.renderer = Renderer(device=self.device, width=width, height=height, stream=stream)
         self.renderer.bind_external_hdr(self.hdr.data_ptr())
         self.width, self.height = width, height
-        self.sample_count = 0
+        self._depth, self._flags = 50, 0
+        self._acc = ShardedAccumulator(self.hdr, lambda first, n: self.renderer.render(n, self._depth, self._flags, first_sample=first), group)
+        self.rank, self.world = self._acc.rank, self._acc.world
+
+    @property
+    def sample_count(self) -> int:
+        return self._acc.sample_count
 
     def set_scene(self, scene) -> None:
         self.renderer.set_scene(scene)
@@ -59,20 +90,13 @@ class ShardedRenderer:
         self.renderer.set_camera(camera)
 
     def clear(self) -> None:
-        self.hdr.zero_()
-        self.sample_count = 0
+        self._acc.clear()
 
     def render(self, spp: int, max_depth: int = 50, flags: int = 0, first_sample: Optional[int] = None, reduce: bool = True):
         """Renders this rank's share of frames [first, first + spp) and (optionally) reduces onto rank 0.
-        After a reduce, rank 0's buffer holds the whole job's sum; the other ranks' buffers hold their shares."""
-        first = self.sample_count + 1 if first_sample is None else first_sample
-        my_first, my_spp = shard_samples(first, spp, self.rank, self.world)
-        if my_spp > 0:
-            self.renderer.render(my_spp, max_depth, flags, first_sample=my_first)
-        if reduce:
-            reduce_hdr(self.hdr, 0, self.group)
-        self.sample_count += spp
-        return self.hdr
+        After a reduce, rank 0's buffer holds the whole job's sum; the other ranks' buffers hold their last share."""
+        self._depth, self._flags = max_depth, flags
+        return self._acc.render(spp, first_sample, reduce)
 
 
 def render_sharded_with(render_fn: Callable[[int, int], "object"], first_sample: int, spp: int, group=None):

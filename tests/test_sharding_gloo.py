@@ -64,6 +64,50 @@ def _worker(rank, world, port, w, h, first, spp, out_path):
     dist.destroy_process_group()
 
 
+def _worker_multicall(rank, world, port, w, h, calls, out_path):
+    sys.path.insert(0, ROOT)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    import torch
+    import torch.distributed as dist
+    import cpuraytracer_b200 as rt
+    from cpuraytracer_b200.distributed import ShardedAccumulator
+    from oracle import orc
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    scene = rt.scenes.scene_small()
+    osc = orc.Scene.from_flat(scene.export())
+    cam = rt.scenes.default_camera(aspect=w / h)
+    cp = orc.camera_params(cam.origin, cam.look_at, cam.vertical_fov, cam.aspect_ratio, cam.focal_length, cam.aperture)
+    hdr_np = np.zeros((h, w, 4), np.float32)
+    hdr = torch.from_numpy(hdr_np)                       # shares memory: the oracle adds into the tensor gloo reduces
+
+    def render_into(my_first, my_spp):
+        orc.render(osc, cp, orc.config(w, h, spp=my_spp, first_sample=my_first, threads=1), hdr_np)
+
+    acc = ShardedAccumulator(hdr, render_into)
+    for spp in calls:
+        acc.render(spp)
+    if rank == 0:
+        np.save(out_path, hdr_np)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_consecutive_sharded_calls_accumulate_once(orc, rt, tmp_path):
+    """bench.py's loop: several render+reduce calls in a row.  Rank 0 must end with every frame exactly once."""
+    import torch.multiprocessing as mp
+    w, h, calls = 40, 24, (3, 2, 4)
+    out = str(tmp_path / "sum.npy")
+    mp.spawn(_worker_multicall, args=(2, _free_port(), w, h, calls, out), nprocs=2, join=True)
+    got = np.load(out)
+    scene = rt.scenes.scene_small()
+    osc = orc.Scene.from_flat(scene.export())
+    cam = rt.scenes.default_camera(aspect=w / h)
+    cp = orc.camera_params(cam.origin, cam.look_at, cam.vertical_fov, cam.aspect_ratio, cam.focal_length, cam.aperture)
+    ref, _ = orc.render(osc, cp, orc.config(w, h, spp=sum(calls), first_sample=1, threads=1))
+    assert np.all(got[..., 3] == sum(calls))
+    assert np.allclose(got, ref, rtol=2e-6, atol=1e-9)
+
+
 @pytest.mark.parametrize("world,spp", [(2, 6), (3, 7), (2, 1)])
 def test_sample_split_plus_reduce_equals_single_rank(orc, rt, tmp_path, world, spp):
     import torch.multiprocessing as mp
