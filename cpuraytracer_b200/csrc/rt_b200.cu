@@ -236,7 +236,7 @@ struct rt_context {
     // instrumentation
     std::vector<EventPair> pending; std::vector<EventPair> pool;
     double render_ms = 0, resolve_ms = 0; int launches = 0;
-    u64 stat_base[4] = {0, 0, 0, 0};
+    u64 stat_base[5] = {0, 0, 0, 0, 0};
     int render_blocks_per_sm = 0, tpb = 256;
 
     float4* hdr() const { return hdr_ext ? hdr_ext : hdr_own; }
@@ -597,12 +597,13 @@ int rt_get_stats(rt_context* c, rt_stats* out) {
     if (int r = ctx_use(c)) return r;
     RT_CUDA(cudaStreamSynchronize(c->stream));
     ev_collect(c);
-    u64 h[5] = {0, 0, 0, 0, 0};
-    RT_CUDA(cudaMemcpy(h, c->counters, 5 * sizeof(u64), cudaMemcpyDeviceToHost));
+    u64 h[6] = {0, 0, 0, 0, 0, 0};
+    RT_CUDA(cudaMemcpy(h, c->counters, 6 * sizeof(u64), cudaMemcpyDeviceToHost));
     memset(out, 0, sizeof *out);
     out->closest_rays = h[1] - c->stat_base[0]; out->shadow_rays = h[2] - c->stat_base[1];
     out->passes = h[3] - c->stat_base[2]; out->paths = h[4] - c->stat_base[3];
-    out->sphere_tests = static_cast<u64>(c->n_spheres) * (out->closest_rays + out->shadow_rays);
+    // tests the device evaluated: shadow rays whose light term is identically zero are answered without a query
+    out->sphere_tests = static_cast<u64>(c->n_spheres) * (out->closest_rays + out->shadow_rays - (h[5] - c->stat_base[4]));
     out->render_ms = c->render_ms; out->resolve_ms = c->resolve_ms;
     out->sm_count = c->prop.multiProcessorCount; out->clock_khz = c->clock_khz; out->launches = c->launches;
     return RT_OK;
@@ -612,9 +613,9 @@ int rt_stats_reset(rt_context* c) {
     if (int r = ctx_use(c)) return r;
     RT_CUDA(cudaStreamSynchronize(c->stream));
     ev_collect(c);
-    u64 h[5];
-    RT_CUDA(cudaMemcpy(h, c->counters, 5 * sizeof(u64), cudaMemcpyDeviceToHost));
-    for (int k = 0; k < 4; ++k) c->stat_base[k] = h[k + 1];
+    u64 h[6];
+    RT_CUDA(cudaMemcpy(h, c->counters, 6 * sizeof(u64), cudaMemcpyDeviceToHost));
+    for (int k = 0; k < 5; ++k) c->stat_base[k] = h[k + 1];
     c->render_ms = c->resolve_ms = 0; c->launches = 0;
     return RT_OK;
 }

@@ -32,7 +32,7 @@ struct RenderParams {
     float4* hdr;                 // running sum, m_backbufferHdr
     float4* partial;             // [n_chunks][W*H] when n_chunks > 1
     u64* work_counter;
-    u64* stats;                  // [0] closest rays [1] shadow rays [2] warp passes [3] paths
+    u64* stats;                  // [0] closest rays [1] shadow rays [2] warp passes [3] paths [4] shadow rays answered without a query
 };
 
 #define RT_FLAG_JITTER_OFF_ 1u
@@ -65,20 +65,19 @@ __device__ __forceinline__ void stage_scene(const RenderParams& p, float4*& sA, 
 
 // Unshadowed DirectionalLight::Shade (light.cpp:20-40) for one light; the occlusion test is resolved by the
 // next fused pass (the shadow ray shares its origin with the scattered ray).
-__device__ __forceinline__ V3 direct_unshadowed(const RenderParams& p, const DevMat& m, V3 pos, V3 n, float u, float v) {
+__device__ __forceinline__ V3 direct_unshadowed(const RenderParams& p, const DevMat& m, V3 pos, V3 n, float u, float v, float n_dot_l) {
     V3 albedo = mk3(0.f, 0.f, 0.f), f0 = mk3(0.04f, 0.04f, 0.04f);            // material.h:27-29,43-45,60-62
     if (m.kind == 0) albedo = texture_rgb(m, u, v);
     else if (m.kind == 1) f0 = texture_rgb(m, u, v);
     const float s = m.smoothness;
     const V3 L = mk3(p.Lx, p.Ly, p.Lz);
-    const float n_dot_l = saturate1(dot3(n, L));                               // light.cpp:26
     const V3 rin = mk3(p.lcx * n_dot_l, p.lcy * n_dot_l, p.lcz * n_dot_l);     // :27
     const V3 view = normalize3(mk3(p.cam.ox, p.cam.oy, p.cam.oz) - pos);       // :33 (camera origin, spheres-app.cpp:250)
     const V3 half = normalize3(L + view);                                      // :34
     const float n_dot_h = saturate1(dot3(n, half));                            // :35
     const float n_dot_v = saturate1(dot3(view, n));                            // :36
     const float pw5 = pow5(1.0f - n_dot_v);
-    const float pw = powf(n_dot_h, s);                                         // :38
+    const float pw = pow_lobe(n_dot_h, s);                                     // :38
     const float k = s + 8.f;
     const V3 refl = mk3(f0.x + (1.0f - f0.x) * pw5, f0.y + (1.0f - f0.y) * pw5, f0.z + (1.0f - f0.z) * pw5);   // :37
     const V3 spec = mk3(((refl.x * 0.125f) * k) * pw, ((refl.y * 0.125f) * k) * pw, ((refl.z * 0.125f) * k) * pw);
@@ -156,7 +155,7 @@ __global__ void RT_RENDER_BOUNDS rt_render_kernel(const RenderParams p) {
     V3 o = mk3(0.f, 0.f, 0.f), d = mk3(0.f, 0.f, 1.f);
     V3 T = mk3(1.f, 1.f, 1.f), Lsum = mk3(0.f, 0.f, 0.f), pend = mk3(0.f, 0.f, 0.f);
     bool want_closest = false, want_shadow = false;
-    uint32_t n_closest = 0, n_shadow = 0, n_pass = 0, n_paths = 0;
+    uint32_t n_closest = 0, n_shadow = 0, n_pass = 0, n_paths = 0, n_skip = 0;
 
     for (;;) {
         // ---- work distribution: warp-aggregated fetch from the global queue ----
@@ -185,8 +184,8 @@ __global__ void RT_RENDER_BOUNDS rt_render_kernel(const RenderParams p) {
             float jx = 0.f, jy = 0.f, lx = 0.f, ly = 0.f;
             if (!(p.flags & RT_FLAG_JITTER_OFF_)) { const float2 j = __ldg(&p.jitter[s_cur]); jx = j.x; jy = j.y; }
             if (!(p.flags & RT_FLAG_LENS_OFF_)) { const float2 l = __ldg(&p.lens[s_cur + px + py]); lx = l.x; ly = l.y; }
-            const float u = (static_cast<float>(px) + jx) / static_cast<float>(p.W);     // spheres-app.cpp:149
-            const float v = (static_cast<float>(py) + jy) / static_cast<float>(p.H);     // :150
+            const float u = div_rn(static_cast<float>(px) + jx, static_cast<float>(p.W));   // spheres-app.cpp:149
+            const float v = div_rn(static_cast<float>(py) + jy, static_cast<float>(p.H));   // :150
             camera_get_ray(p.cam, u, v, lx, ly, o, d);
             T = mk3(1.f, 1.f, 1.f); Lsum = mk3(0.f, 0.f, 0.f);
             depth = 0; want_closest = true; want_shadow = false;
@@ -224,7 +223,12 @@ __global__ void RT_RENDER_BOUNDS rt_render_kernel(const RenderParams p) {
                         rng_counter(static_cast<uint32_t>(pix), p.first_sample + static_cast<u64>(s_cur), static_cast<uint32_t>(depth), p.seed, xi, u1, u2);
                         scattered = scatter(m, d, pos, n, tu, tv, xi, u1, u2, atten, nd);      // :246
                     }
-                    if (has_light) { pend = T * direct_unshadowed(p, m, pos, n, tu, tv); want_shadow = true; }   // :250
+                    if (has_light) {                                                     // :250
+                        const float n_dot_l = saturate1(dot3(n, Ldir));                  // light.cpp:26
+                        if (n_dot_l > 0.f) { pend = T * direct_unshadowed(p, m, pos, n, tu, tv, n_dot_l); want_shadow = true; }
+                        else { ++n_shadow; ++n_skip; }   // facing away: radianceIn == 0 (light.cpp:27), so the term is 0 whether or not the
+                                             // reference's shadow ray (:13-15) is occluded; the ray is counted, not traced
+                    }
                     o = pos;
                     if (cont && scattered) { T = T * atten; d = nd; ++depth; }           // :251
                     else want_closest = false;
@@ -245,11 +249,15 @@ __global__ void RT_RENDER_BOUNDS rt_render_kernel(const RenderParams p) {
     }
 
     // ---- stats: warp reduce, one atomic per warp ----
-    u64 c0 = n_closest, c1 = n_shadow, c3 = n_paths;
+    u64 c0 = n_closest, c1 = n_shadow, c3 = n_paths, c4 = n_skip;
     for (int off = 16; off > 0; off >>= 1) {
         c0 += __shfl_down_sync(FULL, c0, off); c1 += __shfl_down_sync(FULL, c1, off); c3 += __shfl_down_sync(FULL, c3, off);
+        c4 += __shfl_down_sync(FULL, c4, off);
     }
-    if (lane == 0) { atomicAdd(&p.stats[0], c0); atomicAdd(&p.stats[1], c1); atomicAdd(&p.stats[2], static_cast<u64>(n_pass)); atomicAdd(&p.stats[3], c3); }
+    if (lane == 0) {
+        atomicAdd(&p.stats[0], c0); atomicAdd(&p.stats[1], c1); atomicAdd(&p.stats[2], static_cast<u64>(n_pass)); atomicAdd(&p.stats[3], c3);
+        atomicAdd(&p.stats[4], c4);
+    }
 }
 
 // hdr[p] = ((hdr[p] + partial[0][p]) + partial[1][p]) + ...   (fixed order => deterministic)
@@ -303,8 +311,8 @@ __global__ void __launch_bounds__(RT_MAX_TPB) rt_primary_kernel(const RenderPara
             float jx = 0.f, jy = 0.f, lx = 0.f, ly = 0.f;
             if (!(p.flags & RT_FLAG_JITTER_OFF_)) { const float2 j = __ldg(&p.jitter[0]); jx = j.x; jy = j.y; }
             if (!(p.flags & RT_FLAG_LENS_OFF_)) { const float2 l = __ldg(&p.lens[px + py]); lx = l.x; ly = l.y; }
-            const float u = (static_cast<float>(px) + jx) / static_cast<float>(p.W);
-            const float v = (static_cast<float>(py) + jy) / static_cast<float>(p.H);
+            const float u = div_rn(static_cast<float>(px) + jx, static_cast<float>(p.W));
+            const float v = div_rn(static_cast<float>(py) + jy, static_cast<float>(p.H));
             camera_get_ray(p.cam, u, v, lx, ly, o, d);
         }
         const QueryResult q = fused_query<NO_CULL>(sA, sB, sC, sR, lists, static_cast<int>(blockDim.x), p.n_groups, p.n_spheres, o, d, mk3(p.Lx, p.Ly, p.Lz), valid, false);

@@ -65,7 +65,7 @@ typedef struct rt_stats {
     uint64_t paths;            /* path samples traced since the last rt_stats_reset            */
     uint64_t closest_rays;     /* closest-hit queries (GetClosestIntersection, spheres-app.cpp:224) */
     uint64_t shadow_rays;      /* occlusion queries (light.cpp:13-15)                          */
-    uint64_t sphere_tests;     /* n_spheres * (closest_rays + shadow_rays)                     */
+    uint64_t sphere_tests;     /* n_spheres * (closest + shadow queries the device evaluated)   */
     uint64_t passes;           /* warp-level fused passes executed (diagnostic)                */
     double   render_ms;        /* CUDA-event time of the render kernels since the last reset   */
     double   resolve_ms;       /* CUDA-event time of the resolve kernels                       */

@@ -209,7 +209,7 @@ def test_converged_image_matches_reference_sampler(gpu, orc, scene_factory):
     """GPU (counter RNG, brute force) vs the oracle in the reference's own configuration (per-material atomic
     Halton counters, BVH, recursive integrator).  Reported beside the oracle-vs-oracle noise floor (two seeds)."""
     rt = gpu
-    w, h, spp = 160, 90, 1024
+    w, h, spp = 128, 72, 4096          # BASELINE.json: converged linear radiance at 4096 spp
     scene, osc = scene_factory("d488")
     cam = rt.scenes.default_camera()
     r = _renderer(rt, scene, cam, w, h)
