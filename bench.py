@@ -141,7 +141,7 @@ def run_reference(args):
                        "spp_per_step": 1, "note": "the reference's Win32/Direct2D shell cannot build here; its common-lib sources can: " + CPU_NOTE[kind]},
             "cpu_baseline": {"value": value, "unit": "path samples/s", "cores": cores, "kind": kind, "sample": sample},
             "e2e": {"value": value, "unit": "path samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    _emit(line)
     return 0
 
 
@@ -323,14 +323,27 @@ def run_b200(args):
         }
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(args.workload, args.cpu_seconds)
-        print(json.dumps(line), flush=True)
+        _emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
     return 0
 
 
+def _emit(line: dict) -> None:
+    """The ONE JSON line goes to the process's original stdout; everything else (NCCL's version banner, warnings of
+    libraries that print to fd 1) was redirected to stderr by main()."""
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
+
+
+_REAL_STDOUT = 1
+
+
 def main():
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)                       # native libraries (NCCL) write banners to fd 1: keep stdout clean for the JSON line
     args = parse_args()
     if args.impl == "reference":
         return run_reference(args)
