@@ -16,8 +16,11 @@
 #include <cstring>
 #include <iostream>
 #include <sstream>
+#include <unistd.h>
 
 using namespace rtb200;
+
+static FILE* g_json_out = stdout;   // the process's original stdout; fd 1 itself is pointed at stderr (NCCL prints its banner there)
 
 namespace AppSettings {                          // spheres-app.h:5-13 (compile-time there, run-time here)
 struct Settings {
@@ -228,7 +231,7 @@ public:
         rt_stats st{};
         uint64_t closest = 0, shadow = 0;
         for (int i = 0; i < rt_group_size(m_group); ++i) { check(rt_get_stats(rt_group_member(m_group, i), &st)); closest += st.closest_rays; shadow += st.shadow_rays; }
-        std::printf("{\"scene\": \"%s\", \"width\": %d, \"height\": %d, \"spp\": %zu, \"max_depth\": %d, \"gpus\": %d, \"paths\": %zu, \"closest_rays\": %llu, "
+        std::fprintf(g_json_out, "{\"scene\": \"%s\", \"width\": %d, \"height\": %d, \"spp\": %zu, \"max_depth\": %d, \"gpus\": %d, \"paths\": %zu, \"closest_rays\": %llu, "
                     "\"shadow_rays\": %llu, \"seconds\": %.6f, \"path_samples_per_s\": %.6e, \"rays_per_s\": %.6e}\n",
                     m_cfg.sceneFile.empty() ? m_cfg.scene.c_str() : m_cfg.sceneFile.c_str(), m_cfg.backbufferWidth, m_cfg.backbufferHeight, m_sampleCount, m_cfg.recursionDepth,
                     m_cfg.gpus, paths, static_cast<unsigned long long>(closest), static_cast<unsigned long long>(shadow), m_totalTimeInSeconds,
@@ -305,11 +308,16 @@ int main(int argc, char** argv) {
         }
         if (!s.selftest.empty()) return selftest_sinks(s.selftest);
         if (s.backbufferWidth <= 0 || s.backbufferHeight <= 0 || s.spp < 0 || s.recursionDepth < 0 || s.gpus < 1) throw Error(RT_ERR_INVALID_ARGUMENT, "bad size / spp / depth / gpus");
+        std::fflush(stdout);
+        g_json_out = fdopen(dup(1), "w");
+        dup2(2, 1);
         SpheresApp app(s);
         app.OnInitialize();
         if (!s.dumpScene.empty()) { app.DumpSceneFile(s.dumpScene); if (s.spp == 0) return 0; }
         app.CreateDevices();               // fails loudly without a CUDA device: there is no CPU fallback
-        return app.Run();
+        const int rc = app.Run();
+        std::fflush(g_json_out);
+        return rc;
     } catch (const std::exception& e) {
         std::fprintf(stderr, "spheres: error: %s\n", e.what());
         return 2;
