@@ -8,6 +8,7 @@
 //        -shared -o librt_b200.so rt_b200.cu
 #include "../../include/rt_b200.h"
 #include "rt_kernels.cuh"
+#include "rt_wavefront.cuh"
 
 #include <algorithm>
 #include <cmath>
@@ -220,6 +221,9 @@ struct rt_context {
     int clock_khz = 0;
     // scene
     float4 *cullA = nullptr, *cullB = nullptr; float2* cullC = nullptr; float* radius = nullptr; rt::DevMat* mats = nullptr;
+    float4* geom = nullptr;
+    // wavefront layout (RT_FLAG_WAVEFRONT): SoA path state, allocated on first use
+    rt::WfState wf{}; void* wf_block = nullptr; unsigned int* wf_live = nullptr; int wf_bps = 0;
     int n_spheres = 0, n_pad = 0;
     bool scene_set = false, camera_set = false;
     rt::RenderParams base{};
@@ -305,6 +309,7 @@ void rt_context_destroy(rt_context* c) {
     cudaStreamSynchronize(c->stream);
     ev_collect(c);
     for (auto& e : c->pool) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
+    cudaFree(c->geom); cudaFree(c->wf_block); cudaFree(c->wf_live);
     cudaFree(c->cullA); cudaFree(c->cullB); cudaFree(c->cullC); cudaFree(c->radius); cudaFree(c->mats);
     cudaFree(c->hdr_own); cudaFree(c->ldr); cudaFree(c->ids); cudaFree(c->mids); cudaFree(c->partial);
     cudaFree(c->jitter); cudaFree(c->lens); cudaFree(c->counters);
@@ -383,6 +388,10 @@ int rt_set_scene(rt_context* c, const rt_scene* s) {
     if (int r = dev_realloc(c->cullC, np)) return r;
     if (int r = dev_realloc(c->radius, n_pad)) return r;
     if (int r = dev_realloc(c->mats, M.size())) return r;
+    std::vector<float4> G(std::max(n, 1), make_float4(0.f, 0.f, 0.f, 1.f));
+    for (int i = 0; i < n; ++i) G[i] = make_float4(s->spheres[i].cx, s->spheres[i].cy, s->spheres[i].cz, s->spheres[i].radius);
+    if (int r = dev_realloc(c->geom, G.size())) return r;
+    RT_CUDA(cudaMemcpyAsync(c->geom, G.data(), G.size() * sizeof(float4), cudaMemcpyHostToDevice, c->stream));
     RT_CUDA(cudaMemcpyAsync(c->cullA, A.data(), np * sizeof(float4), cudaMemcpyHostToDevice, c->stream));
     RT_CUDA(cudaMemcpyAsync(c->cullB, B.data(), np * sizeof(float4), cudaMemcpyHostToDevice, c->stream));
     RT_CUDA(cudaMemcpyAsync(c->cullC, C.data(), np * sizeof(float2), cudaMemcpyHostToDevice, c->stream));
@@ -390,7 +399,7 @@ int rt_set_scene(rt_context* c, const rt_scene* s) {
     RT_CUDA(cudaMemcpyAsync(c->mats, M.data(), M.size() * sizeof(rt::DevMat), cudaMemcpyHostToDevice, c->stream));
     RT_CUDA(cudaStreamSynchronize(c->stream));
     rt::RenderParams& b = c->base;
-    b.cullA = c->cullA; b.cullB = c->cullB; b.cullC = c->cullC; b.radius = c->radius; b.mats = c->mats;
+    b.cullA = c->cullA; b.cullB = c->cullB; b.cullC = c->cullC; b.radius = c->radius; b.mats = c->mats; b.sphere_geom = c->geom;
     b.n_spheres = n; b.n_pairs_pad = np; b.n_groups = n_pad / 32; b.n_lights = has_light ? 1 : 0;
     b.Lx = b.Ly = b.Lz = 0.f; b.lcx = b.lcy = b.lcz = 0.f;
     if (has_light) {
@@ -409,6 +418,8 @@ int rt_set_scene(rt_context* c, const rt_scene* s) {
     RT_CUDA(cudaFuncSetAttribute(rt::rt_render_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
     RT_CUDA(cudaFuncSetAttribute(rt::rt_primary_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
     RT_CUDA(cudaFuncSetAttribute(rt::rt_primary_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
+    RT_CUDA(cudaFuncSetAttribute(rt::wf_intersect_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
+    RT_CUDA(cudaFuncSetAttribute(rt::wf_intersect_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
     int best_tpb = 0, best_bps = 0;
     for (int tpb = 256; tpb <= RT_MAX_TPB; tpb += 256) {
         const size_t smem = cta_smem_bytes(n_pad, tpb);
@@ -420,6 +431,8 @@ int rt_set_scene(rt_context* c, const rt_scene* s) {
     if (best_bps < 1) return fail(RT_ERR_UNSUPPORTED, "rt_set_scene: render kernel does not fit on an SM with %zu B shared memory", cta_smem_bytes(n_pad, 256));
     c->tpb = best_tpb;
     c->render_blocks_per_sm = best_bps;
+    RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&c->wf_bps, rt::wf_intersect_kernel<false>, best_tpb, cta_smem_bytes(n_pad, best_tpb)));
+    if (c->wf_bps < 1) c->wf_bps = 1;
     return RT_OK;
 }
 
@@ -495,11 +508,51 @@ static int prepare_frames(rt_context* c, u64 first_sample, int spp, int max_dept
     return RT_OK;
 }
 
+// Wavefront schedule of one rt_render call: intersect / shade kernels over SoA path state until the work queue drains.
+static int render_wavefront(rt_context* c, const rt::RenderParams& p, uint32_t flags) {
+    const u64 n_items = static_cast<u64>(p.tiles_x) * p.tiles_y * 32ull * static_cast<u64>(p.n_chunks);
+    const int want = static_cast<int>(std::min<u64>(n_items, 1ull << 21));
+    if (c->wf.n_slots != want) {
+        if (c->wf_block) { cudaFree(c->wf_block); c->wf_block = nullptr; c->wf.n_slots = 0; }
+        const size_t per = static_cast<size_t>(want) * 16;                       // every array is 16 B per slot
+        RT_CUDA(cudaMalloc(&c->wf_block, per * 7));
+        char* b = static_cast<char*>(c->wf_block);
+        c->wf.o = reinterpret_cast<float4*>(b); c->wf.d = reinterpret_cast<float4*>(b + per); c->wf.thr = reinterpret_cast<float4*>(b + 2 * per);
+        c->wf.rad = reinterpret_cast<float4*>(b + 3 * per); c->wf.pend = reinterpret_cast<float4*>(b + 4 * per);
+        c->wf.acc = reinterpret_cast<float4*>(b + 5 * per); c->wf.ids = reinterpret_cast<int4*>(b + 6 * per);
+        c->wf.n_slots = want;
+    }
+    if (!c->wf_live) RT_CUDA(cudaMalloc(&c->wf_live, sizeof(unsigned int)));
+    RT_CUDA(cudaMemsetAsync(c->wf.ids, 0, static_cast<size_t>(want) * 16, c->stream));       // all slots: "no path yet"
+    const size_t smem = cta_smem_bytes(c->n_pad, c->tpb);
+    const int grid_i = c->prop.multiProcessorCount * c->wf_bps;
+    const int grid_s = c->prop.multiProcessorCount * 8;
+    rt::wf_shade_kernel<<<grid_s, 256, 0, c->stream>>>(p, c->wf, nullptr);                     // fetch work + primary rays
+    ++c->launches;
+    const int kBatch = 16;
+    for (int round = 0; round < (1 << 20); ++round) {
+        for (int k = 0; k < kBatch; ++k) {
+            if (flags & RT_FLAG_DEBUG_NO_CULL_) rt::wf_intersect_kernel<true><<<grid_i, c->tpb, smem, c->stream>>>(p, c->wf);
+            else rt::wf_intersect_kernel<false><<<grid_i, c->tpb, smem, c->stream>>>(p, c->wf);
+            const bool last = (k == kBatch - 1);
+            if (last) RT_CUDA(cudaMemsetAsync(c->wf_live, 0, sizeof(unsigned int), c->stream));
+            rt::wf_shade_kernel<<<grid_s, 256, 0, c->stream>>>(p, c->wf, last ? c->wf_live : nullptr);
+            c->launches += 2;
+        }
+        unsigned int live = 0;
+        RT_CUDA(cudaMemcpyAsync(&live, c->wf_live, sizeof live, cudaMemcpyDeviceToHost, c->stream));
+        RT_CUDA(cudaStreamSynchronize(c->stream));
+        if (live == 0) return RT_OK;
+    }
+    return fail(RT_ERR_CUDA, "rt_render (wavefront): the work queue did not drain");
+}
+
 int rt_render(rt_context* c, uint64_t first_sample, int spp, int max_depth, uint32_t flags) {
     if (!c) return fail(RT_ERR_INVALID_ARGUMENT, "rt_render: ctx is NULL");
     if (!c->scene_set || !c->camera_set || !c->hdr()) return fail(RT_ERR_NOT_READY, "rt_render: scene, camera and framebuffer must be set first");
     if (first_sample < 1 || spp < 0 || max_depth < 0) return fail(RT_ERR_INVALID_ARGUMENT, "rt_render: first_sample >= 1, spp >= 0, max_depth >= 0 required");
-    if (flags & ~(RT_FLAG_JITTER_OFF | RT_FLAG_LENS_OFF | RT_FLAG_DEBUG_NO_CULL_)) return fail(RT_ERR_INVALID_ARGUMENT, "rt_render: unknown flag bits 0x%x", flags);
+    if (flags & ~(RT_FLAG_JITTER_OFF | RT_FLAG_LENS_OFF | RT_FLAG_WAVEFRONT | RT_FLAG_DEBUG_NO_CULL_)) return fail(RT_ERR_INVALID_ARGUMENT, "rt_render: unknown flag bits 0x%x", flags);
+    if ((flags & RT_FLAG_WAVEFRONT) && max_depth >= (1 << 22)) return fail(RT_ERR_INVALID_ARGUMENT, "rt_render: the wavefront layout packs the depth into 23 bits");
     if (spp == 0) return RT_OK;
     if (int r = ctx_use(c)) return r;
     rt::RenderParams p;
@@ -523,9 +576,12 @@ int rt_render(rt_context* c, uint64_t first_sample, int spp, int max_depth, uint
     const size_t smem = cta_smem_bytes(c->n_pad, c->tpb);
     const int grid = c->prop.multiProcessorCount * c->render_blocks_per_sm;
     EventPair ev = ev_begin(c, 0);
-    if (flags & RT_FLAG_DEBUG_NO_CULL_) rt::rt_render_kernel<true><<<grid, c->tpb, smem, c->stream>>>(p);
-    else rt::rt_render_kernel<false><<<grid, c->tpb, smem, c->stream>>>(p);
-    ++c->launches;
+    if (flags & RT_FLAG_WAVEFRONT) { if (int r = render_wavefront(c, p, flags)) return r; }
+    else {
+        if (flags & RT_FLAG_DEBUG_NO_CULL_) rt::rt_render_kernel<true><<<grid, c->tpb, smem, c->stream>>>(p);
+        else rt::rt_render_kernel<false><<<grid, c->tpb, smem, c->stream>>>(p);
+        ++c->launches;
+    }
     if (p.n_chunks > 1) {
         rt::rt_combine_kernel<<<static_cast<unsigned>((n_pix + 255) / 256), 256, 0, c->stream>>>(p.hdr, p.partial, p.n_chunks, n_pix);
         ++c->launches;

@@ -15,6 +15,7 @@ struct RenderParams {
     // scene (global memory; the cull arrays are staged into shared memory by every CTA)
     const float4* cullA; const float4* cullB; const float2* cullC; const float* radius;
     const DevMat* mats;
+    const float4* sphere_geom;   // (cx, cy, cz, radius) per sphere, for kernels that do not stage the scene (wavefront shade)
     int n_spheres, n_pairs_pad, n_groups;
     int n_lights;
     float Lx, Ly, Lz;            // normalised light direction (light.cpp:7)
@@ -37,6 +38,7 @@ struct RenderParams {
 
 #define RT_FLAG_JITTER_OFF_ 1u
 #define RT_FLAG_LENS_OFF_ 2u
+#define RT_FLAG_WAVEFRONT_ 4u
 #define RT_FLAG_DEBUG_NO_CULL_ 0x100u
 
 enum LaneState { ST_NEED_ITEM = 0, ST_NEW_PATH = 1, ST_IN_PATH = 2, ST_DONE = 3 };

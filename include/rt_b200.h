@@ -59,7 +59,9 @@ typedef struct rt_camera_basis { float origin[3], x[3], y[3], image_origin[3]; f
 
 /* render flags */
 enum { RT_FLAG_JITTER_OFF = 1u,   /* jitterOffset = 0 (spheres-app.cpp:140)              */
-       RT_FLAG_LENS_OFF = 2u };   /* lens offset = 0  (spheres-app.cpp:152): pinhole rays */
+       RT_FLAG_LENS_OFF = 2u,     /* lens offset = 0  (spheres-app.cpp:152): pinhole rays */
+       RT_FLAG_WAVEFRONT = 4u };  /* schedule the same work as separate intersect / shade kernels over SoA path state in HBM
+                                     (same bits as the default megakernel; kept for the measured layout comparison) */
 
 typedef struct rt_stats {
     uint64_t paths;            /* path samples traced since the last rt_stats_reset            */

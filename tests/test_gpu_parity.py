@@ -229,3 +229,29 @@ def test_converged_image_matches_reference_sampler(gpu, orc, scene_factory):
           f"mean rel err {mean_rel_err(g, ref):.5f}")
     assert mean_rel_err(g, ref) < 5e-3                  # BASELINE: image-mean relative error < 0.5 %
     assert got < 1.5 * floor + 1e-2                     # within Monte Carlo noise of the faithful sampler at this spp
+
+
+# ---------------------------------------------------------------- wavefront layout == megakernel, bit for bit
+@pytest.mark.parametrize("name,w,h,spp,depth,flags", [
+    ("small", 160, 90, 4, 50, 0),
+    ("d488", 250, 141, 3, 50, 0),          # ragged tiles
+    ("d488", 192, 108, 40, 50, 0),         # spp > 16: chunked work items + combine
+    ("d488", 192, 108, 2, 0, 3),           # direct only, pinhole
+])
+def test_wavefront_layout_equals_megakernel(gpu, scene_factory, name, w, h, spp, depth, flags):
+    """RT_FLAG_WAVEFRONT schedules the same work items as separate intersect / shade kernels over SoA path state in HBM:
+    same device functions, same accumulation order => identical running sums and identical ray counts."""
+    rt = gpu
+    scene, _ = scene_factory(name)
+    cam = rt.scenes.default_camera(aspect=w / h)
+    r = _renderer(rt, scene, cam, w, h)
+    r.reset_stats()
+    r.render(spp, depth, flags)
+    a, sa = r.read_hdr_sum(), r.stats()
+    r.clear()
+    r.reset_stats()
+    r.render(spp, depth, flags | rt.RT_FLAG_WAVEFRONT)
+    b, sb = r.read_hdr_sum(), r.stats()
+    assert np.array_equal(a, b)
+    assert (sa.paths, sa.closest_rays, sa.shadow_rays, sa.sphere_tests) == (sb.paths, sb.closest_rays, sb.shadow_rays, sb.sphere_tests)
+    assert sb.launches > sa.launches

@@ -6,6 +6,8 @@ import sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import cpuraytracer_b200 as rt
 
+FLAGS = int(os.environ.get("RT_PROBE_FLAGS", "0"), 0)     # e.g. 4 = RT_FLAG_WAVEFRONT
+
 CASES = [("d488", 1920, 1080, 64, 50), ("d488", 1920, 1080, 64, 0), ("s4096", 1920, 1080, 8, 50)]
 if len(sys.argv) > 1:
     CASES = [c for c in CASES if c[0] in sys.argv[1:]]
@@ -13,13 +15,13 @@ for name, w, h, spp, depth in CASES:
     r = rt.Renderer(0, w, h)
     r.set_scene(rt.scenes.NAMED[name]())
     r.set_camera(rt.scenes.default_camera(aspect=w / h))
-    r.render(spp, depth)
+    r.render(spp, depth, FLAGS)
     r.synchronize()
     best = None
     for _ in range(3):
         r.clear()
         r.reset_stats()
-        r.render(spp, depth)
+        r.render(spp, depth, FLAGS)
         st = r.stats()
         if best is None or st.render_ms < best.render_ms:
             best = st
