@@ -13,7 +13,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(CSRC, "librt_b200.so")
-SOURCES = ["rt_b200.cu", "rt_kernels.cuh", "rt_device.cuh"]
+SOURCES = ["rt_b200.cu", "rt_kernels.cuh", "rt_device.cuh", "rt_bvh.cuh", "rt_wavefront.cuh"]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

@@ -240,8 +240,11 @@ struct rt_context {
     // instrumentation
     std::vector<EventPair> pending; std::vector<EventPair> pool;
     double render_ms = 0, resolve_ms = 0; int launches = 0;
-    u64 stat_base[5] = {0, 0, 0, 0, 0};
+    u64 stat_base[6] = {0, 0, 0, 0, 0, 0};
     int render_blocks_per_sm = 0, tpb = 256;
+    // RT_FLAG_ACCEL: shared-memory image of the box hierarchy (rt_bvh.cuh), built by rt_set_scene
+    uint4* accel_blob = nullptr; bool accel_ok = false; std::string accel_why;
+    int accel_tpb = 0, accel_bps = 0;
 
     float4* hdr() const { return hdr_ext ? hdr_ext : hdr_own; }
 };
@@ -277,6 +280,161 @@ static size_t scene_smem_bytes(int n_pad) { return static_cast<size_t>(n_pad / 2
 // scene arrays + the per-thread candidate lists (2 lists x RT_LIST_CAP words), see stage_scene()
 static size_t cta_smem_bytes(int n_pad, int tpb) { return scene_smem_bytes(n_pad) + static_cast<size_t>(tpb) * 2u * RT_LIST_CAP * 4u; }
 
+// ------------------------------------------------------------------------------------------------
+// RT_FLAG_ACCEL: host build of the box hierarchy image (layout + conservativeness argument: rt_bvh.cuh).
+// The reference builds its BVH in BvhNode::BvhNode (ray-tracing.cpp:107-167: median split on a random axis);
+// here the order is a Morton sort, the tree is implicit (32 spheres per group, 8 groups per L2 node) and the
+// image is position-independent so every CTA copies it verbatim into shared memory.
+// ------------------------------------------------------------------------------------------------
+static size_t accel_cta_smem_bytes(const rt::AccelParams& a, int tpb) {
+    return static_cast<size_t>(a.blob_bytes) + static_cast<size_t>(tpb) * (a.gmask_words + 2 * RT_ACCEL_ENTRY_CAP) * 4u;
+}
+static uint32_t morton_spread10(uint32_t v) {
+    v = (v | (v << 16)) & 0x030000FFu; v = (v | (v << 8)) & 0x0300F00Fu;
+    v = (v | (v << 4)) & 0x030C30C3u; v = (v | (v << 2)) & 0x09249249u;
+    return v;
+}
+static float round_up(double x) { float f = static_cast<float>(x); if (static_cast<double>(f) < x) f = std::nextafter(f, INFINITY); return f; }
+
+static int build_accel(rt_context* c, const rt_scene* s) {
+    c->accel_ok = false; c->accel_why.clear();
+    rt::AccelParams& a = c->base.accel;
+    a = rt::AccelParams{};
+    const int n = static_cast<int>(s->spheres.size());
+    if (n > 65000) { c->accel_why = "more than 65000 spheres (slot -> index map is 16 bit)"; return RT_OK; }
+    // big spheres: radius > 4 x median (at most 64, the largest first)
+    std::vector<float> radii(n);
+    for (int i = 0; i < n; ++i) radii[i] = s->spheres[i].radius;
+    std::vector<int> big, small;
+    if (n > 0) {
+        std::vector<float> sorted = radii; std::sort(sorted.begin(), sorted.end());
+        float thr = 4.f * sorted[n / 2];
+        const int over = static_cast<int>(sorted.end() - std::upper_bound(sorted.begin(), sorted.end(), thr));
+        if (over > 64) thr = sorted[n - 65];
+        for (int i = 0; i < n; ++i) (radii[i] > thr ? big : small).push_back(i);
+    }
+    // Morton order of the small spheres' centres (10 bits per axis inside their bounding box)
+    double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
+    for (int i : small) { const rt_sphere_desc& sp = s->spheres[i]; const double cc[3] = {sp.cx, sp.cy, sp.cz};
+        for (int k = 0; k < 3; ++k) { lo[k] = std::min(lo[k], cc[k]); hi[k] = std::max(hi[k], cc[k]); } }
+    std::vector<std::pair<uint32_t, int>> keyed;
+    for (int i : small) {
+        const rt_sphere_desc& sp = s->spheres[i]; const double cc[3] = {sp.cx, sp.cy, sp.cz};
+        uint32_t q[3];
+        for (int k = 0; k < 3; ++k) { const double e = hi[k] - lo[k]; q[k] = e > 0 ? static_cast<uint32_t>(std::min(1023.0, (cc[k] - lo[k]) / e * 1024.0)) : 0u; }
+        keyed.push_back({morton_spread10(q[0]) | (morton_spread10(q[1]) << 1) | (morton_spread10(q[2]) << 2), i});
+    }
+    std::stable_sort(keyed.begin(), keyed.end(), [](const std::pair<uint32_t, int>& x, const std::pair<uint32_t, int>& y) { return x.first < y.first; });
+    const int n_big_groups = (static_cast<int>(big.size()) + 31) / 32;
+    const int n_groups = (static_cast<int>(small.size()) + 31) / 32;
+    const int n2 = (n_groups + 7) / 8;
+    if (n2 > 32) { c->accel_why = "more than 8192 small spheres (the L2 mask is one 32-bit word)"; return RT_OK; }
+    const int n_slots = (n_big_groups + n_groups) * 32;
+    std::vector<int> slot_orig(std::max(n_slots, 1), -1);
+    for (size_t k = 0; k < big.size(); ++k) slot_orig[k] = big[k];
+    for (size_t k = 0; k < keyed.size(); ++k) slot_orig[n_big_groups * 32 + k] = keyed[k].second;
+    const int np = n_slots / 2;
+    // sections
+    auto align16 = [](size_t x) { return (x + 15u) & ~static_cast<size_t>(15u); };
+    const size_t off_A = 0, off_B = off_A + static_cast<size_t>(np) * 16, off_R = off_B + static_cast<size_t>(np) * 16;
+    const size_t off_I = align16(off_R + static_cast<size_t>(n_slots) * 4);
+    const size_t off_box = align16(off_I + static_cast<size_t>(n_slots) * 2);
+    const size_t off_top = off_box + static_cast<size_t>(n2) * RT_ACCEL_NODE_FLOATS * 4;
+    const size_t total = std::max<size_t>(16, off_top + static_cast<size_t>(n2) * 32);
+    std::vector<unsigned char> img(total, 0);
+    float* A = reinterpret_cast<float*>(img.data() + off_A); float* B = reinterpret_cast<float*>(img.data() + off_B);
+    float* R = reinterpret_cast<float*>(img.data() + off_R); uint16_t* I = reinterpret_cast<uint16_t*>(img.data() + off_I);
+    float* BOX = reinterpret_cast<float*>(img.data() + off_box); float* TOP = reinterpret_cast<float*>(img.data() + off_top);
+    const double K = static_cast<double>(RT_CULL_K);
+    for (int slot = 0; slot < n_slots; ++slot) {
+        const int p = slot >> 1, h = slot & 1, i = slot_orig[slot];
+        float cx = 0.f, cy = 0.f, cz = 0.f, wn = RT_PAD_W, r = 0.f;
+        if (i >= 0) {
+            const rt_sphere_desc& sp = s->spheres[i];
+            cx = sp.cx; cy = sp.cy; cz = sp.cz; r = sp.radius;
+            const double cc = static_cast<double>(sp.cx) * sp.cx + static_cast<double>(sp.cy) * sp.cy + static_cast<double>(sp.cz) * sp.cz;
+            const double r2 = static_cast<double>(sp.radius) * sp.radius;
+            wn = static_cast<float>(r2 - cc + K * (cc + r2));
+        }
+        A[p * 4 + h] = cx; A[p * 4 + 2 + h] = cy; B[p * 4 + h] = cz; B[p * 4 + 2 + h] = wn;
+        R[slot] = r; I[slot] = i >= 0 ? static_cast<uint16_t>(i) : 0xFFFFu;
+    }
+    // boxes
+    struct Box { double lo[3], hi[3]; bool any; };
+    auto empty_box = []() { Box b; for (int k = 0; k < 3; ++k) { b.lo[k] = 1e300; b.hi[k] = -1e300; } b.any = false; return b; };
+    auto grow = [](Box& b, const Box& o) { if (!o.any) return; for (int k = 0; k < 3; ++k) { b.lo[k] = std::min(b.lo[k], o.lo[k]); b.hi[k] = std::max(b.hi[k], o.hi[k]); } b.any = true; };
+    auto to_ch = [](const Box& b, float* cxyz, float* hxyz) {
+        if (!b.any) { for (int k = 0; k < 3; ++k) { cxyz[k] = 0.f; hxyz[k] = -1.0e30f; } return; }
+        for (int k = 0; k < 3; ++k) {
+            const float cf = static_cast<float>(0.5 * (b.lo[k] + b.hi[k]));
+            cxyz[k] = cf; hxyz[k] = round_up(std::max(b.hi[k] - static_cast<double>(cf), static_cast<double>(cf) - b.lo[k]));
+        }
+    };
+    std::vector<Box> gbox(n2 * 8, empty_box());
+    Box all = empty_box();
+    double r_min = 1e300, r_max = 0;
+    for (int g = 0; g < n_groups; ++g)
+        for (int j = 0; j < 32; ++j) {
+            const int i = slot_orig[(n_big_groups + g) * 32 + j];
+            if (i < 0) continue;
+            const rt_sphere_desc& sp = s->spheres[i];
+            Box b; b.any = true; const double cc[3] = {sp.cx, sp.cy, sp.cz};
+            for (int k = 0; k < 3; ++k) { b.lo[k] = cc[k] - sp.radius; b.hi[k] = cc[k] + sp.radius; }
+            grow(gbox[g], b);
+            r_min = std::min<double>(r_min, sp.radius); r_max = std::max<double>(r_max, sp.radius);
+        }
+    for (int j2 = 0; j2 < n2; ++j2) {
+        Box node = empty_box();
+        float* blk = BOX + static_cast<size_t>(j2) * RT_ACCEL_NODE_FLOATS;
+        for (int k = 0; k < 8; ++k) {
+            const Box& b = gbox[j2 * 8 + k];
+            grow(node, b);
+            float cc[3], hh[3]; to_ch(b, cc, hh);
+            blk[k] = cc[0]; blk[8 + k] = cc[1]; blk[16 + k] = cc[2]; blk[24 + k] = hh[0]; blk[32 + k] = hh[1]; blk[40 + k] = hh[2];
+        }
+        float cc[3], hh[3]; to_ch(node, cc, hh);
+        float* t = TOP + static_cast<size_t>(j2) * 8;
+        t[0] = cc[0]; t[1] = cc[1]; t[2] = cc[2]; t[3] = hh[0]; t[4] = hh[1]; t[5] = hh[2];
+        grow(all, node);
+    }
+    a.csx = a.csy = a.csz = 0.f; a.cs_radius = 0.f; a.r_min = 1.f; a.r_max = 1.f; a.c_max = 0.f;
+    if (all.any) {
+        const double cs[3] = {0.5 * (all.lo[0] + all.hi[0]), 0.5 * (all.lo[1] + all.hi[1]), 0.5 * (all.lo[2] + all.hi[2])};
+        a.csx = static_cast<float>(cs[0]); a.csy = static_cast<float>(cs[1]); a.csz = static_cast<float>(cs[2]);
+        double rad = 0, cmax = 0;
+        for (int i : small) {
+            const rt_sphere_desc& sp = s->spheres[i];
+            const double dx = sp.cx - static_cast<double>(a.csx), dy = sp.cy - static_cast<double>(a.csy), dz = sp.cz - static_cast<double>(a.csz);
+            rad = std::max(rad, std::sqrt(dx * dx + dy * dy + dz * dz) + sp.radius);
+        }
+        for (int k = 0; k < 3; ++k) cmax = std::max(cmax, std::max(std::fabs(all.lo[k]), std::fabs(all.hi[k])));
+        a.cs_radius = round_up(rad * (1.0 + 1e-6)); a.c_max = round_up(cmax);
+        a.r_min = static_cast<float>(r_min); a.r_max = static_cast<float>(r_max);
+    }
+    if (int r = dev_realloc(c->accel_blob, total / 16)) return r;
+    RT_CUDA(cudaMemcpyAsync(c->accel_blob, img.data(), total, cudaMemcpyHostToDevice, c->stream));
+    RT_CUDA(cudaStreamSynchronize(c->stream));
+    a.blob = c->accel_blob; a.blob_bytes = static_cast<int>(total);
+    a.off_B = static_cast<int>(off_B); a.off_R = static_cast<int>(off_R); a.off_I = static_cast<int>(off_I);
+    a.off_box = static_cast<int>(off_box); a.off_top = static_cast<int>(off_top);
+    a.n_pairs = np; a.n_big_groups = n_big_groups; a.n_groups = n_groups; a.n2 = n2; a.gmask_words = std::max(1, (n2 + 3) / 4);
+    // CTA size: most resident warps per SM next to one image copy per CTA
+    const int optin = static_cast<int>(c->prop.sharedMemPerBlockOptin);
+    RT_CUDA(cudaFuncSetAttribute(rt::rt_render_kernel<rt::MODE_ACCEL>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
+    RT_CUDA(cudaFuncSetAttribute(rt::rt_primary_kernel<rt::MODE_ACCEL>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
+    int best_tpb = 0, best_bps = 0;
+    for (int tpb = 128; tpb <= RT_ACCEL_MAX_TPB; tpb += 128) {
+        const size_t smem = accel_cta_smem_bytes(a, tpb);
+        if (smem > static_cast<size_t>(optin)) break;
+        int bps = 0;
+        RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, rt::rt_render_kernel<rt::MODE_ACCEL>, tpb, smem));
+        if (bps * tpb > best_bps * best_tpb) { best_tpb = tpb; best_bps = bps; }
+    }
+    if (best_bps < 1) { c->accel_why = "the hierarchy image does not fit in shared memory"; return RT_OK; }
+    c->accel_tpb = best_tpb; c->accel_bps = best_bps; c->accel_ok = true;
+    return RT_OK;
+}
+
 extern "C" {
 
 int rt_context_create(int device, rt_context** out) {
@@ -309,7 +467,7 @@ void rt_context_destroy(rt_context* c) {
     cudaStreamSynchronize(c->stream);
     ev_collect(c);
     for (auto& e : c->pool) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
-    cudaFree(c->geom); cudaFree(c->wf_block); cudaFree(c->wf_live);
+    cudaFree(c->geom); cudaFree(c->wf_block); cudaFree(c->wf_live); cudaFree(c->accel_blob);
     cudaFree(c->cullA); cudaFree(c->cullB); cudaFree(c->cullC); cudaFree(c->radius); cudaFree(c->mats);
     cudaFree(c->hdr_own); cudaFree(c->ldr); cudaFree(c->ids); cudaFree(c->mids); cudaFree(c->partial);
     cudaFree(c->jitter); cudaFree(c->lens); cudaFree(c->counters);
@@ -414,10 +572,10 @@ int rt_set_scene(rt_context* c, const rt_scene* s) {
     // opt in to large dynamic shared memory; pick the CTA size that keeps the most warps resident per SM (one scene copy per
     // CTA, so big scenes want big CTAs) and size the persistent grid to exactly fill the machine
     const int optin = static_cast<int>(c->prop.sharedMemPerBlockOptin);
-    RT_CUDA(cudaFuncSetAttribute(rt::rt_render_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
-    RT_CUDA(cudaFuncSetAttribute(rt::rt_render_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
-    RT_CUDA(cudaFuncSetAttribute(rt::rt_primary_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
-    RT_CUDA(cudaFuncSetAttribute(rt::rt_primary_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
+    RT_CUDA(cudaFuncSetAttribute(rt::rt_render_kernel<rt::MODE_CULL>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
+    RT_CUDA(cudaFuncSetAttribute(rt::rt_render_kernel<rt::MODE_NO_CULL>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
+    RT_CUDA(cudaFuncSetAttribute(rt::rt_primary_kernel<rt::MODE_CULL>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
+    RT_CUDA(cudaFuncSetAttribute(rt::rt_primary_kernel<rt::MODE_NO_CULL>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
     RT_CUDA(cudaFuncSetAttribute(rt::wf_intersect_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
     RT_CUDA(cudaFuncSetAttribute(rt::wf_intersect_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
     int best_tpb = 0, best_bps = 0;
@@ -425,7 +583,7 @@ int rt_set_scene(rt_context* c, const rt_scene* s) {
         const size_t smem = cta_smem_bytes(n_pad, tpb);
         if (smem > static_cast<size_t>(optin)) break;
         int bps = 0;
-        RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, rt::rt_render_kernel<false>, tpb, smem));
+        RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, rt::rt_render_kernel<rt::MODE_CULL>, tpb, smem));
         if (bps * tpb > best_bps * best_tpb) { best_tpb = tpb; best_bps = bps; }
     }
     if (best_bps < 1) return fail(RT_ERR_UNSUPPORTED, "rt_set_scene: render kernel does not fit on an SM with %zu B shared memory", cta_smem_bytes(n_pad, 256));
@@ -433,7 +591,9 @@ int rt_set_scene(rt_context* c, const rt_scene* s) {
     c->render_blocks_per_sm = best_bps;
     RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&c->wf_bps, rt::wf_intersect_kernel<false>, best_tpb, cta_smem_bytes(n_pad, best_tpb)));
     if (c->wf_bps < 1) c->wf_bps = 1;
-    return RT_OK;
+    auto safe_inv = [](float d) { const float dd = std::fabs(d) < 1e-18f ? std::copysign(1e-18f, d) : d; return 1.0f / dd; };   // rt_bvh.cuh safe_inv
+    b.iLx = safe_inv(b.Lx); b.iLy = safe_inv(b.Ly); b.iLz = safe_inv(b.Lz);
+    return build_accel(c, s);
 }
 
 int rt_set_camera(rt_context* c, const rt_camera_params* cam) {
@@ -551,7 +711,9 @@ int rt_render(rt_context* c, uint64_t first_sample, int spp, int max_depth, uint
     if (!c) return fail(RT_ERR_INVALID_ARGUMENT, "rt_render: ctx is NULL");
     if (!c->scene_set || !c->camera_set || !c->hdr()) return fail(RT_ERR_NOT_READY, "rt_render: scene, camera and framebuffer must be set first");
     if (first_sample < 1 || spp < 0 || max_depth < 0) return fail(RT_ERR_INVALID_ARGUMENT, "rt_render: first_sample >= 1, spp >= 0, max_depth >= 0 required");
-    if (flags & ~(RT_FLAG_JITTER_OFF | RT_FLAG_LENS_OFF | RT_FLAG_WAVEFRONT | RT_FLAG_DEBUG_NO_CULL_)) return fail(RT_ERR_INVALID_ARGUMENT, "rt_render: unknown flag bits 0x%x", flags);
+    if (flags & ~(RT_FLAG_JITTER_OFF | RT_FLAG_LENS_OFF | RT_FLAG_WAVEFRONT | RT_FLAG_ACCEL | RT_FLAG_DEBUG_NO_CULL_)) return fail(RT_ERR_INVALID_ARGUMENT, "rt_render: unknown flag bits 0x%x", flags);
+    if ((flags & RT_FLAG_ACCEL) && (flags & (RT_FLAG_WAVEFRONT | RT_FLAG_DEBUG_NO_CULL_))) return fail(RT_ERR_INVALID_ARGUMENT, "rt_render: RT_FLAG_ACCEL cannot be combined with the wavefront layout or the no-cull debug mode");
+    if ((flags & RT_FLAG_ACCEL) && !c->accel_ok) return fail(RT_ERR_UNSUPPORTED, "rt_render: RT_FLAG_ACCEL unavailable for this scene: %s", c->accel_why.c_str());
     if ((flags & RT_FLAG_WAVEFRONT) && max_depth >= (1 << 22)) return fail(RT_ERR_INVALID_ARGUMENT, "rt_render: the wavefront layout packs the depth into 23 bits");
     if (spp == 0) return RT_OK;
     if (int r = ctx_use(c)) return r;
@@ -577,9 +739,12 @@ int rt_render(rt_context* c, uint64_t first_sample, int spp, int max_depth, uint
     const int grid = c->prop.multiProcessorCount * c->render_blocks_per_sm;
     EventPair ev = ev_begin(c, 0);
     if (flags & RT_FLAG_WAVEFRONT) { if (int r = render_wavefront(c, p, flags)) return r; }
-    else {
-        if (flags & RT_FLAG_DEBUG_NO_CULL_) rt::rt_render_kernel<true><<<grid, c->tpb, smem, c->stream>>>(p);
-        else rt::rt_render_kernel<false><<<grid, c->tpb, smem, c->stream>>>(p);
+    else if (flags & RT_FLAG_ACCEL) {
+        rt::rt_render_kernel<rt::MODE_ACCEL><<<c->prop.multiProcessorCount * c->accel_bps, c->accel_tpb, accel_cta_smem_bytes(p.accel, c->accel_tpb), c->stream>>>(p);
+        ++c->launches;
+    } else {
+        if (flags & RT_FLAG_DEBUG_NO_CULL_) rt::rt_render_kernel<rt::MODE_NO_CULL><<<grid, c->tpb, smem, c->stream>>>(p);
+        else rt::rt_render_kernel<rt::MODE_CULL><<<grid, c->tpb, smem, c->stream>>>(p);
         ++c->launches;
     }
     if (p.n_chunks > 1) {
@@ -639,8 +804,10 @@ int rt_primary_hits(rt_context* c, uint64_t sample, uint32_t flags, int32_t* sph
     p.chunk_spp = 1; p.n_chunks = 1;
     const size_t smem = cta_smem_bytes(c->n_pad, c->tpb);
     const int grid = c->prop.multiProcessorCount * std::max(1, c->render_blocks_per_sm);
-    if (flags & RT_FLAG_DEBUG_NO_CULL_) rt::rt_primary_kernel<true><<<grid, c->tpb, smem, c->stream>>>(p, c->ids, c->mids);
-    else rt::rt_primary_kernel<false><<<grid, c->tpb, smem, c->stream>>>(p, c->ids, c->mids);
+    if ((flags & RT_FLAG_ACCEL) && !c->accel_ok) return fail(RT_ERR_UNSUPPORTED, "rt_primary_hits: RT_FLAG_ACCEL unavailable for this scene: %s", c->accel_why.c_str());
+    if (flags & RT_FLAG_ACCEL) rt::rt_primary_kernel<rt::MODE_ACCEL><<<c->prop.multiProcessorCount * c->accel_bps, c->accel_tpb, accel_cta_smem_bytes(p.accel, c->accel_tpb), c->stream>>>(p, c->ids, c->mids);
+    else if (flags & RT_FLAG_DEBUG_NO_CULL_) rt::rt_primary_kernel<rt::MODE_NO_CULL><<<grid, c->tpb, smem, c->stream>>>(p, c->ids, c->mids);
+    else rt::rt_primary_kernel<rt::MODE_CULL><<<grid, c->tpb, smem, c->stream>>>(p, c->ids, c->mids);
     ++c->launches;
     RT_CUDA(cudaGetLastError());
     if (sphere_idx) RT_CUDA(cudaMemcpyAsync(sphere_idx, c->ids, n * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
@@ -653,13 +820,13 @@ int rt_get_stats(rt_context* c, rt_stats* out) {
     if (int r = ctx_use(c)) return r;
     RT_CUDA(cudaStreamSynchronize(c->stream));
     ev_collect(c);
-    u64 h[6] = {0, 0, 0, 0, 0, 0};
-    RT_CUDA(cudaMemcpy(h, c->counters, 6 * sizeof(u64), cudaMemcpyDeviceToHost));
+    u64 h[7] = {0, 0, 0, 0, 0, 0, 0};
+    RT_CUDA(cudaMemcpy(h, c->counters, 7 * sizeof(u64), cudaMemcpyDeviceToHost));
     memset(out, 0, sizeof *out);
     out->closest_rays = h[1] - c->stat_base[0]; out->shadow_rays = h[2] - c->stat_base[1];
     out->passes = h[3] - c->stat_base[2]; out->paths = h[4] - c->stat_base[3];
     // tests the device evaluated: shadow rays whose light term is identically zero are answered without a query
-    out->sphere_tests = static_cast<u64>(c->n_spheres) * (out->closest_rays + out->shadow_rays - (h[5] - c->stat_base[4]));
+    out->sphere_tests = h[6] - c->stat_base[5];
     out->render_ms = c->render_ms; out->resolve_ms = c->resolve_ms;
     out->sm_count = c->prop.multiProcessorCount; out->clock_khz = c->clock_khz; out->launches = c->launches;
     return RT_OK;
@@ -669,9 +836,9 @@ int rt_stats_reset(rt_context* c) {
     if (int r = ctx_use(c)) return r;
     RT_CUDA(cudaStreamSynchronize(c->stream));
     ev_collect(c);
-    u64 h[6];
-    RT_CUDA(cudaMemcpy(h, c->counters, 6 * sizeof(u64), cudaMemcpyDeviceToHost));
-    for (int k = 0; k < 5; ++k) c->stat_base[k] = h[k + 1];
+    u64 h[7];
+    RT_CUDA(cudaMemcpy(h, c->counters, 7 * sizeof(u64), cudaMemcpyDeviceToHost));
+    for (int k = 0; k < 6; ++k) c->stat_base[k] = h[k + 1];
     c->render_ms = c->resolve_ms = 0; c->launches = 0;
     return RT_OK;
 }

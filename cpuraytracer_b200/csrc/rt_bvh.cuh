@@ -1,0 +1,243 @@
+// rt_bvh.cuh -- RT_FLAG_ACCEL: a two-level bounding-box hierarchy in shared memory in front of the same cull + exact tests
+// (the reference's own closest-hit query walks a BVH, ray-tracing.cpp:107-214).
+//
+// Brute force (rt_device.cuh, fused_query) stays the parity ground truth; this path must return the SAME bits:
+//   * the spheres are re-ordered on the host (rt_b200.cu, build_accel): "big" spheres first (radius > 4 x median -- the
+//     r = 1000 ground would bloat every box that contains it), then the rest in Morton order of their centres;
+//     32 consecutive slots form a GROUP (the unit of the candidate masks), 8 consecutive groups an L2 NODE;
+//   * a group is visited when the closest ray or the shadow ray touches its (padded) bounding box; visited groups go
+//     through the SAME conservative FFMA2 discriminant cull as brute force, and every candidate through the SAME exact
+//     Sphere::Intersect restatement (sphere_exact), so an accepted hit has the reference's t bit for bit;
+//   * the winner is chosen by `closer()` (smaller t, then smaller ORIGINAL index), which does not depend on visiting order.
+// So the only way to differ from brute force is to skip a group that holds a sphere the exact test accepts.  The box test
+// is made conservative against that with a per-ray pad (see box_ray()); tests/test_gpu_parity.py compares whole renders,
+// hit buffers and ray counters of both modes bit for bit.
+//
+// Schedule of one query (per lane; lanes of a warp run the same phase together):
+//   T  top             converged loop over the n2 L2 boxes                       -> bit mask m2 of touched L2 nodes
+//   M  middle          per lane: pop an L2 node, test its 8 group boxes          -> one byte per L2 node in shared memory
+//   G  groups          the big groups first (every lane, same addresses: broadcast LDS), then per lane: pop a touched group,
+//                      cull its 16 sphere pairs for both rays (pair order rotated by the lane id so that the quarter-warps'
+//                      LDS.128 hit 8 different bank groups)                      -> candidate-mask entries
+//   E  exact           per lane: walk the entries, exact test per candidate
+#pragma once
+#include "rt_device.cuh"
+
+namespace rt {
+
+// Everything the kernel needs to find the sections of the shared-memory image (built on the host, copied verbatim).
+struct AccelParams {
+    const uint4* blob;       // device copy of the image
+    int blob_bytes;          // multiple of 16
+    int off_B, off_R, off_I, off_box, off_top;   // byte offsets of the sections (A starts at 0)
+    int n_pairs;             // sphere pairs in the image (big groups + small groups, each padded to 32 slots)
+    int n_big_groups;        // groups that are always culled
+    int n_groups;            // small groups (Morton order)
+    int n2;                  // L2 nodes = ceil(n_groups / 8), <= 32
+    int gmask_words;         // per-thread scratch words holding one byte per L2 node
+    float csx, csy, csz, cs_radius;   // bounding sphere of the small spheres (centres + radii)
+    float r_min, r_max;               // smallest / largest radius among the small spheres
+    float c_max;                      // largest |coordinate| of any small-sphere box face
+};
+
+#define RT_ACCEL_ENTRY_CAP 8          /* candidate-mask entries (2 words each) per lane; a full list is drained (E) before G goes on */
+#define RT_ACCEL_NODE_FLOATS 52       /* 8 children x (cx,cy,cz,hx,hy,hz) SoA = 48 floats, padded to 13 float4 (bank skew) */
+
+struct AccelSmem {
+    const float4* sA; const float4* sB; const float* sR; const uint16_t* sI;
+    const float* box;        // [n2][RT_ACCEL_NODE_FLOATS]
+    const float4* top;       // [n2][2]: (cx,cy,cz,hx) (hy,hz,-,-)
+    uint32_t* scratch;       // this thread's column: word w at scratch[w * blockDim.x]
+};
+
+__device__ __forceinline__ AccelSmem stage_accel(const AccelParams& a, unsigned char* smem) {
+    uint4* dst = reinterpret_cast<uint4*>(smem);
+    const int n16 = a.blob_bytes >> 4;
+    for (int i = threadIdx.x; i < n16; i += blockDim.x) dst[i] = a.blob[i];
+    __syncthreads();
+    AccelSmem s;
+    s.sA = reinterpret_cast<const float4*>(smem);
+    s.sB = reinterpret_cast<const float4*>(smem + a.off_B);
+    s.sR = reinterpret_cast<const float*>(smem + a.off_R);
+    s.sI = reinterpret_cast<const uint16_t*>(smem + a.off_I);
+    s.box = reinterpret_cast<const float*>(smem + a.off_box);
+    s.top = reinterpret_cast<const float4*>(smem + a.off_top);
+    s.scratch = reinterpret_cast<uint32_t*>(smem + a.blob_bytes) + threadIdx.x;
+    return s;
+}
+
+// Conservative discriminant signs of one sphere pair for both rays; as cull_pair() but (o-c).L is evaluated with three
+// FMAs from the centre instead of being read from a per-light array (the image carries no light-dependent data).
+struct CullRay2 { float ox2, oy2, oz2, ndx, ndy, ndz, nLx, nLy, nLz, noo, od, oL; };
+__device__ __forceinline__ void cull_pair2(const CullRay2& r, const float4 A, const float4 B, uint32_t& mc, uint32_t& ms) {
+    const u64 cx = pk2(A.x, A.y), cy = pk2(A.z, A.w), cz = pk2(B.x, B.y);
+    u64 nc2 = fadd2(pk2(B.z, B.w), bc2(r.noo));
+    nc2 = ffma2(bc2(r.oz2), cz, nc2); nc2 = ffma2(bc2(r.oy2), cy, nc2); nc2 = ffma2(bc2(r.ox2), cx, nc2);
+    u64 b1 = ffma2(bc2(r.ndz), cz, bc2(r.od)); b1 = ffma2(bc2(r.ndy), cy, b1); b1 = ffma2(bc2(r.ndx), cx, b1);
+    u64 b2 = ffma2(bc2(r.nLz), cz, bc2(r.oL)); b2 = ffma2(bc2(r.nLy), cy, b2); b2 = ffma2(bc2(r.nLx), cx, b2);
+    const u64 d1 = ffma2(b1, b1, nc2);
+    const u64 d2 = ffma2(b2, b2, nc2);
+    uint32_t lo, hi;
+    upk2(d1, lo, hi); mc = __funnelshift_l(lo, mc, 1); mc = __funnelshift_l(hi, mc, 1);
+    upk2(d2, lo, hi); ms = __funnelshift_l(lo, ms, 1); ms = __funnelshift_l(hi, ms, 1);
+}
+
+// Slab test constants of one ray.  A box (centre c, half extent h) is touched when, per axis k,
+//     tn_k = (c_k - o_k) inv_k - (h_k + pad) |inv_k|,   tf_k = (c_k - o_k) inv_k + (h_k + pad) |inv_k|,
+//     max_k tn_k <= min_k tf_k   and   min_k tf_k >= -t_slack.
+// `pad` makes the test conservative against everything the exact test can accept:
+//   (1) Sphere::Intersect in binary32 accepts a ray whose true distance p to the centre satisfies p^2 < r^2 + E, where E
+//       bounds the rounding of disc = b*b - a*c (ray-tracing.cpp:44-50): |error| <= 16 ulp-units of |oc|^2 + r^2.  With the
+//       ray's distance to any small sphere <= Dmax = |o - Cs| + Rs this is E <= 2^-18 (Dmax^2 + r_max^2) (4x margin), i.e. the
+//       line passes within sqrt(r^2 + E) - r <= min(E / 2r_min, sqrt(E)) of the sphere: first pad term (x1.5);
+//   (2) the slab arithmetic itself (one rounding of o_k*inv_k, one of the FMA) moves a plane by at most
+//       2^-23 (|o_k| + |c_k|) in world units: second pad term 2^-19 (|o|_1 + c_max).
+// The accepted root exceeds the 0.001 bias (ray-tracing.cpp:58,71) and the far root of the inflated sphere is not smaller
+// than the computed one (up to the rounding of b, <= 2^-22 Dmax), hence tf >= -t_slack with t_slack = 2^-16 Dmax.
+// Directions with |d_k| < 1e-18 use 1e-18 (both slabs then span the whole axis unless the origin is outside them).
+struct BoxRay { float ix, iy, iz, ax, ay, az, nx, ny, nz, fx, fy, fz; };
+__device__ __forceinline__ float safe_inv(float d) {
+    const float dd = fabsf(d) < 1e-18f ? copysignf(1e-18f, d) : d;
+    return 1.0f / dd;
+}
+__device__ __forceinline__ BoxRay box_ray(V3 o, float ix, float iy, float iz, float pad) {
+    BoxRay r;
+    r.ix = ix; r.iy = iy; r.iz = iz;
+    r.ax = fabsf(ix); r.ay = fabsf(iy); r.az = fabsf(iz);
+    const float nox = -(o.x * ix), noy = -(o.y * iy), noz = -(o.z * iz);
+    const float ex = pad * r.ax, ey = pad * r.ay, ez = pad * r.az;
+    r.nx = nox - ex; r.ny = noy - ey; r.nz = noz - ez;
+    r.fx = nox + ex; r.fy = noy + ey; r.fz = noz + ez;
+    return r;
+}
+__device__ __forceinline__ bool box_touched(const BoxRay& r, float cx, float cy, float cz, float hx, float hy, float hz, float neg_t_slack) {
+    const float tnx = fmaf(-hx, r.ax, fmaf(cx, r.ix, r.nx)), tfx = fmaf(hx, r.ax, fmaf(cx, r.ix, r.fx));
+    const float tny = fmaf(-hy, r.ay, fmaf(cy, r.iy, r.ny)), tfy = fmaf(hy, r.ay, fmaf(cy, r.iy, r.fy));
+    const float tnz = fmaf(-hz, r.az, fmaf(cz, r.iz, r.nz)), tfz = fmaf(hz, r.az, fmaf(cz, r.iz, r.fz));
+    const float tn = fmaxf(fmaxf(tnx, tny), tnz);
+    const float tf = fminf(fminf(tfx, tfy), tfz);
+    return tn <= tf && tf >= neg_t_slack;
+}
+
+struct AccelCounters { uint32_t group_visits; };
+
+// Same contract as fused_query(): closest hit along (o,d) and occlusion along (o,L).  res.idx is the ORIGINAL sphere
+// index, res.slot the position in the re-ordered image (for the hit record's centre / radius).
+__device__ __forceinline__ QueryResult fused_query_accel(const AccelSmem& s, const AccelParams& a, int lstride,
+                                                         V3 o, V3 d, V3 L, V3 invL, bool want_closest, bool want_shadow, AccelCounters& cnt) {
+    QueryResult res; res.t = 0.f; res.idx = -1; res.slot = -1; res.occluded = false;
+    const unsigned lane = threadIdx.x & 31u;
+    const float oo = fmaf(o.x, o.x, fmaf(o.y, o.y, o.z * o.z));
+    CullRay2 cr;
+    cr.ox2 = o.x + o.x; cr.oy2 = o.y + o.y; cr.oz2 = o.z + o.z;
+    cr.ndx = -d.x; cr.ndy = -d.y; cr.ndz = -d.z;
+    cr.nLx = -L.x; cr.nLy = -L.y; cr.nLz = -L.z;
+    cr.noo = fmaf(RT_CULL_K, oo, -oo);
+    cr.od = fmaf(o.x, d.x, fmaf(o.y, d.y, o.z * d.z));
+    cr.oL = fmaf(o.x, L.x, fmaf(o.y, L.y, o.z * L.z));
+    ExactCtx ex;
+    ex.sA = s.sA; ex.sB = s.sB; ex.sR = s.sR; ex.o = o; ex.d = d; ex.L = L;
+    ex.a = dot3(d, d);
+    ex.aL = dot3(L, L);
+    const uint32_t en_c = want_closest ? 0xffffffffu : 0u;
+    uint32_t en_s = want_shadow ? 0xffffffffu : 0u;
+    uint32_t* const gm = s.scratch;                                   // one byte per L2 node
+    uint32_t* const ent = s.scratch + a.gmask_words * lstride;        // entries: (mask, slot_base | shadow << 31)
+
+    // ---- per-ray slab constants ----
+    const float dcx = o.x - a.csx, dcy = o.y - a.csy, dcz = o.z - a.csz;
+    const float dmax = sqrtf(fmaf(dcx, dcx, fmaf(dcy, dcy, dcz * dcz))) + a.cs_radius;
+    const float E = 3.814697265625e-06f * fmaf(dmax, dmax, a.r_max * a.r_max);                       // 2^-18
+    const float pad = 1.5f * fminf(E / (2.0f * a.r_min), sqrtf(E))
+                    + 1.9073486328125e-06f * (fabsf(o.x) + fabsf(o.y) + fabsf(o.z) + a.c_max);      // 2^-19
+    const float neg_t_slack = -1.52587890625e-05f * dmax;                                            // 2^-16
+    const BoxRay rc = box_ray(o, safe_inv(d.x), safe_inv(d.y), safe_inv(d.z), pad);
+    const BoxRay rs = box_ray(o, invL.x, invL.y, invL.z, pad);
+    const bool wc = want_closest, ws = want_shadow;
+
+    // ---- T: L2 boxes, converged ----
+    uint32_t m2 = 0u;
+    for (int j = 0; j < a.n2; ++j) {
+        const float4 b0 = s.top[2 * j], b1 = s.top[2 * j + 1];
+        const bool hit = (wc && box_touched(rc, b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, neg_t_slack)) ||
+                         (ws && box_touched(rs, b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, neg_t_slack));
+        if (hit) m2 |= 1u << j;
+    }
+
+    // ---- M: group boxes of the touched L2 nodes ----
+    uint32_t m2g = 0u;
+    while (m2) {
+        const int j = __ffs(m2) - 1; m2 &= m2 - 1u;
+        const float4* blk = reinterpret_cast<const float4*>(s.box + j * RT_ACCEL_NODE_FLOATS);
+        uint32_t byte = 0u;
+#pragma unroll 1
+        for (int h = 0; h < 2; ++h) {
+            const float4 cx = blk[h], cy = blk[2 + h], cz = blk[4 + h], hx = blk[6 + h], hy = blk[8 + h], hz = blk[10 + h];
+            const float cxa[4] = {cx.x, cx.y, cx.z, cx.w}, cya[4] = {cy.x, cy.y, cy.z, cy.w}, cza[4] = {cz.x, cz.y, cz.z, cz.w};
+            const float hxa[4] = {hx.x, hx.y, hx.z, hx.w}, hya[4] = {hy.x, hy.y, hy.z, hy.w}, hza[4] = {hz.x, hz.y, hz.z, hz.w};
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const bool hit = (wc && box_touched(rc, cxa[k], cya[k], cza[k], hxa[k], hya[k], hza[k], neg_t_slack)) ||
+                                 (ws && box_touched(rs, cxa[k], cya[k], cza[k], hxa[k], hya[k], hza[k], neg_t_slack));
+                if (hit) byte |= 1u << (h * 4 + k);
+            }
+        }
+        if (byte) {
+            m2g |= 1u << j;
+            reinterpret_cast<unsigned char*>(gm + (j >> 2) * lstride)[j & 3] = static_cast<unsigned char>(byte);
+        }
+    }
+
+    // ---- G + E.  One copy of each in the code: G runs until this lane's groups are exhausted or its entry list is
+    // full, E drains the list; the outer loop repeats only after an overflow (rare). ----
+    const int rot_lane = static_cast<int>(lane & 15u);
+    int big = 0;                                            // big groups still to cull (all lanes, first)
+    uint32_t cur8 = 0u; int curj = 0;
+    bool more = true;
+    while (more) {
+        int ne = 0;
+        for (;;) {
+            if (ne > RT_ACCEL_ENTRY_CAP - 2) break;         // a group adds at most two entries
+            int slot_base, rot;
+            if (big < a.n_big_groups) { slot_base = big * 32; rot = 0; ++big; }
+            else {
+                if (cur8 == 0u) {
+                    if (m2g == 0u) { more = false; break; }
+                    curj = __ffs(m2g) - 1; m2g &= m2g - 1u;
+                    cur8 = reinterpret_cast<const unsigned char*>(gm + (curj >> 2) * lstride)[curj & 3];
+                }
+                const int k = __ffs(cur8) - 1; cur8 &= cur8 - 1u;
+                slot_base = (a.n_big_groups + curj * 8 + k) * 32; rot = rot_lane;
+                cnt.group_visits += (en_c & 1u) + (en_s & 1u);
+            }
+            const float4* pa = s.sA + (slot_base >> 1);
+            const float4* pb = s.sB + (slot_base >> 1);
+            uint32_t mc = 0u, ms = 0u;
+#pragma unroll
+            for (int q = 0; q < 16; ++q) { const int qq = (q + rot) & 15; cull_pair2(cr, pa[qq], pb[qq], mc, ms); }
+            mc = __funnelshift_r(mc, mc, 2 * rot); ms = __funnelshift_r(ms, ms, 2 * rot);
+            const uint32_t cc = ~mc & en_c, cs = ~ms & en_s;
+            if (cc) { ent[(2 * ne) * lstride] = cc; ent[(2 * ne + 1) * lstride] = static_cast<uint32_t>(slot_base); ++ne; }
+            if (cs) { ent[(2 * ne) * lstride] = cs; ent[(2 * ne + 1) * lstride] = static_cast<uint32_t>(slot_base) | 0x80000000u; ++ne; }
+        }
+        int e = 0; uint32_t cur = 0u, meta = 0u;
+        for (;;) {
+            if (cur == 0u) {
+                if (e >= ne) break;
+                cur = ent[(2 * e) * lstride]; meta = ent[(2 * e + 1) * lstride]; ++e;
+                if ((meta >> 31) && en_s == 0u) { cur = 0u; continue; }
+            }
+            const int j = __clz(cur); cur &= ~(0x80000000u >> j);
+            const bool sh = (meta >> 31) != 0u;
+            const int slot = static_cast<int>(meta & 0x7fffffffu) + j;
+            float t;
+            if (exact_candidate(ex, slot, sh, t)) {
+                if (sh) { res.occluded = true; en_s = 0u; cur = 0u; }
+                else { const int idx = s.sI[slot]; if (closer(t, idx, res)) { res.t = t; res.idx = idx; res.slot = slot; } }
+            }
+        }
+    }
+    return res;
+}
+
+}  // namespace rt

@@ -8,6 +8,7 @@
 //   rt_primary_kernel  K6: primary-hit sphere / material id buffers.
 #pragma once
 #include "rt_device.cuh"
+#include "rt_bvh.cuh"
 
 namespace rt {
 
@@ -34,11 +35,15 @@ struct RenderParams {
     float4* partial;             // [n_chunks][W*H] when n_chunks > 1
     u64* work_counter;
     u64* stats;                  // [0] closest rays [1] shadow rays [2] warp passes [3] paths [4] shadow rays answered without a query
+                                 // [5] sphere tests evaluated for rays that asked for them (both query modes)
+    AccelParams accel;           // RT_FLAG_ACCEL: box hierarchy image (rt_bvh.cuh)
+    float iLx, iLy, iLz;         // safe_inv of the light direction (slab test of the shadow ray)
 };
 
 #define RT_FLAG_JITTER_OFF_ 1u
 #define RT_FLAG_LENS_OFF_ 2u
 #define RT_FLAG_WAVEFRONT_ 4u
+#define RT_FLAG_ACCEL_ 8u
 #define RT_FLAG_DEBUG_NO_CULL_ 0x100u
 
 enum LaneState { ST_NEED_ITEM = 0, ST_NEW_PATH = 1, ST_IN_PATH = 2, ST_DONE = 3 };
@@ -137,12 +142,22 @@ __device__ __forceinline__ bool item_to_pixel(const RenderParams& p, u64 item, i
     return px < p.W && py < p.H;
 }
 
-template <bool NO_CULL>
-__global__ void RT_RENDER_BOUNDS rt_render_kernel(const RenderParams p) {
+// MODE: 0 = brute force with the conservative cull (default), 1 = brute force, every sphere through the exact test
+// (debug: proves the cull is result-neutral), 2 = RT_FLAG_ACCEL box hierarchy in front of the same cull (rt_bvh.cuh).
+enum { MODE_CULL = 0, MODE_NO_CULL = 1, MODE_ACCEL = 2 };
+#define RT_ACCEL_MAX_TPB 512   /* the hierarchy walk keeps two sets of slab constants live: 128 registers per thread */
+template <int MODE>
+__global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : RT_MAX_TPB) rt_render_kernel(const RenderParams p) {
     extern __shared__ __align__(16) unsigned char smem[];
-    float4 *sA, *sB; float2* sC; float* sR; uint32_t* lists;
-    stage_scene(p, sA, sB, sC, sR, lists, smem);
+    float4 *sA = nullptr, *sB = nullptr; float2* sC = nullptr; float* sR = nullptr; uint32_t* lists = nullptr;
+    AccelSmem av{};
+    if constexpr (MODE == MODE_ACCEL) {
+        av = stage_accel(p.accel, smem);
+        sA = const_cast<float4*>(av.sA); sB = const_cast<float4*>(av.sB); sR = const_cast<float*>(av.sR);
+    } else stage_scene(p, sA, sB, sC, sR, lists, smem);
     const int lstride = static_cast<int>(blockDim.x);
+    const V3 invL = mk3(p.iLx, p.iLy, p.iLz);
+    AccelCounters acnt; acnt.group_visits = 0u;
 
     const unsigned FULL = 0xffffffffu;
     const unsigned lane = threadIdx.x & 31u;
@@ -196,7 +211,9 @@ __global__ void RT_RENDER_BOUNDS rt_render_kernel(const RenderParams p) {
         const bool active = (st == ST_IN_PATH);
 
         // ---- K2+K3: fused closest-hit / shadow query over every sphere ----
-        const QueryResult q = fused_query<NO_CULL>(sA, sB, sC, sR, lists, lstride, p.n_groups, p.n_spheres, o, d, Ldir, active && want_closest, active && want_shadow);
+        QueryResult q;
+        if constexpr (MODE == MODE_ACCEL) q = fused_query_accel(av, p.accel, lstride, o, d, Ldir, invL, active && want_closest, active && want_shadow, acnt);
+        else q = fused_query<MODE == MODE_NO_CULL>(sA, sB, sC, sR, lists, lstride, p.n_groups, p.n_spheres, o, d, Ldir, active && want_closest, active && want_shadow);
         ++n_pass;
 
         // ---- K4: integrate ----
@@ -209,10 +226,10 @@ __global__ void RT_RENDER_BOUNDS rt_render_kernel(const RenderParams p) {
                     Lsum = Lsum + T * sky;
                     want_closest = false;
                 } else {
-                    const int idx = q.idx;
-                    const float* fa = reinterpret_cast<const float*>(sA) + (idx >> 1) * 4 + (idx & 1);
-                    const V3 ctr = mk3(fa[0], fa[2], reinterpret_cast<const float*>(sB)[(idx >> 1) * 4 + (idx & 1)]);
-                    const float radius = sR[idx];
+                    const int idx = q.idx, slot = (MODE == MODE_ACCEL) ? q.slot : q.idx;
+                    const float* fa = reinterpret_cast<const float*>(sA) + (slot >> 1) * 4 + (slot & 1);
+                    const V3 ctr = mk3(fa[0], fa[2], reinterpret_cast<const float*>(sB)[(slot >> 1) * 4 + (slot & 1)]);
+                    const float radius = sR[slot];
                     const V3 pos = mk3(q.t * d.x + o.x, q.t * d.y + o.y, q.t * d.z + o.z);   // ray-tracing.cpp:61
                     const V3 n = (pos - ctr) / radius;                                   // :62
                     const float tu = 0.5f * n.x + 0.5f, tv = 0.5f * n.z + 0.5f;          // :36-37
@@ -252,13 +269,18 @@ __global__ void RT_RENDER_BOUNDS rt_render_kernel(const RenderParams p) {
 
     // ---- stats: warp reduce, one atomic per warp ----
     u64 c0 = n_closest, c1 = n_shadow, c3 = n_paths, c4 = n_skip;
+    // sphere tests evaluated for rays that asked for them: every sphere per query (brute force), or the big spheres plus
+    // 32 per visited group (box hierarchy)
+    u64 c5 = (MODE == MODE_ACCEL)
+        ? static_cast<u64>(p.accel.n_big_groups * 32) * (n_closest + n_shadow - n_skip) + 32ull * acnt.group_visits
+        : static_cast<u64>(p.n_spheres) * (n_closest + n_shadow - n_skip);
     for (int off = 16; off > 0; off >>= 1) {
         c0 += __shfl_down_sync(FULL, c0, off); c1 += __shfl_down_sync(FULL, c1, off); c3 += __shfl_down_sync(FULL, c3, off);
-        c4 += __shfl_down_sync(FULL, c4, off);
+        c4 += __shfl_down_sync(FULL, c4, off); c5 += __shfl_down_sync(FULL, c5, off);
     }
     if (lane == 0) {
         atomicAdd(&p.stats[0], c0); atomicAdd(&p.stats[1], c1); atomicAdd(&p.stats[2], static_cast<u64>(n_pass)); atomicAdd(&p.stats[3], c3);
-        atomicAdd(&p.stats[4], c4);
+        atomicAdd(&p.stats[4], c4); atomicAdd(&p.stats[5], c5);
     }
 }
 
@@ -299,11 +321,14 @@ __global__ void rt_resolve_kernel(const float4* __restrict__ hdr, uint32_t* __re
 }
 
 // K6: primary-hit id buffers (jitter/lens per flags) for frame `first_sample`.
-template <bool NO_CULL>
-__global__ void __launch_bounds__(RT_MAX_TPB) rt_primary_kernel(const RenderParams p, int32_t* __restrict__ sphere_idx, int32_t* __restrict__ material_id) {
+template <int MODE>
+__global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : RT_MAX_TPB) rt_primary_kernel(const RenderParams p, int32_t* __restrict__ sphere_idx, int32_t* __restrict__ material_id) {
     extern __shared__ __align__(16) unsigned char smem[];
-    float4 *sA, *sB; float2* sC; float* sR; uint32_t* lists;
-    stage_scene(p, sA, sB, sC, sR, lists, smem);
+    float4 *sA = nullptr, *sB = nullptr; float2* sC = nullptr; float* sR = nullptr; uint32_t* lists = nullptr;
+    AccelSmem av{};
+    if constexpr (MODE == MODE_ACCEL) av = stage_accel(p.accel, smem);
+    else stage_scene(p, sA, sB, sC, sR, lists, smem);
+    AccelCounters acnt; acnt.group_visits = 0u;
     const u64 n_items = static_cast<u64>(p.tiles_x) * p.tiles_y * 32ull;
     for (u64 item = blockIdx.x * static_cast<u64>(blockDim.x) + threadIdx.x; item < ((n_items + 31ull) & ~31ull); item += static_cast<u64>(gridDim.x) * blockDim.x) {
         int chunk, px, py;
@@ -317,7 +342,9 @@ __global__ void __launch_bounds__(RT_MAX_TPB) rt_primary_kernel(const RenderPara
             const float v = div_rn(static_cast<float>(py) + jy, static_cast<float>(p.H));
             camera_get_ray(p.cam, u, v, lx, ly, o, d);
         }
-        const QueryResult q = fused_query<NO_CULL>(sA, sB, sC, sR, lists, static_cast<int>(blockDim.x), p.n_groups, p.n_spheres, o, d, mk3(p.Lx, p.Ly, p.Lz), valid, false);
+        QueryResult q;
+        if constexpr (MODE == MODE_ACCEL) q = fused_query_accel(av, p.accel, static_cast<int>(blockDim.x), o, d, mk3(p.Lx, p.Ly, p.Lz), mk3(p.iLx, p.iLy, p.iLz), valid, false, acnt);
+        else q = fused_query<MODE == MODE_NO_CULL>(sA, sB, sC, sR, lists, static_cast<int>(blockDim.x), p.n_groups, p.n_spheres, o, d, mk3(p.Lx, p.Ly, p.Lz), valid, false);
         if (valid) {
             const int pix = py * p.W + px;
             if (sphere_idx) sphere_idx[pix] = q.idx;

@@ -175,6 +175,7 @@ __global__ void __launch_bounds__(256) wf_shade_kernel(const RenderParams p, con
         if (c1) atomicAdd(&p.stats[1], c1);
         if (c3) atomicAdd(&p.stats[3], c3);
         if (c4) atomicAdd(&p.stats[4], c4);
+        if (c0 + c1 - c4) atomicAdd(&p.stats[5], static_cast<u64>(p.n_spheres) * (c0 + c1 - c4));
         if (live_out && c5) atomicAdd(live_out, c5);
     }
 }

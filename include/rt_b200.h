@@ -60,8 +60,11 @@ typedef struct rt_camera_basis { float origin[3], x[3], y[3], image_origin[3]; f
 /* render flags */
 enum { RT_FLAG_JITTER_OFF = 1u,   /* jitterOffset = 0 (spheres-app.cpp:140)              */
        RT_FLAG_LENS_OFF = 2u,     /* lens offset = 0  (spheres-app.cpp:152): pinhole rays */
-       RT_FLAG_WAVEFRONT = 4u };  /* schedule the same work as separate intersect / shade kernels over SoA path state in HBM
+       RT_FLAG_WAVEFRONT = 4u,    /* schedule the same work as separate intersect / shade kernels over SoA path state in HBM
                                      (same bits as the default megakernel; kept for the measured layout comparison) */
+       RT_FLAG_ACCEL = 8u };      /* closest-hit / occlusion queries go through a bounding-box hierarchy (what BvhNode::Intersect,
+                                     ray-tracing.cpp:174-214, does in the reference) before the same cull + exact tests; returns the
+                                     same bits as the default brute-force query, only faster on large scenes */
 
 typedef struct rt_stats {
     uint64_t paths;            /* path samples traced since the last rt_stats_reset            */

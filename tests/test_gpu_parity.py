@@ -255,3 +255,68 @@ def test_wavefront_layout_equals_megakernel(gpu, scene_factory, name, w, h, spp,
     assert np.array_equal(a, b)
     assert (sa.paths, sa.closest_rays, sa.shadow_rays, sa.sphere_tests) == (sb.paths, sb.closest_rays, sb.shadow_rays, sb.sphere_tests)
     assert sb.launches > sa.launches
+
+
+# ---------------------------------------------------------------- RT_FLAG_ACCEL (box hierarchy) == brute force, bit for bit
+@pytest.mark.parametrize("name,w,h,spp,depth,flags", [
+    ("small", 160, 90, 4, 50, 0),
+    ("d488", 250, 141, 3, 50, 0),          # ragged tiles
+    ("d488", 192, 108, 40, 50, 0),         # chunked work items + combine
+    ("d488", 192, 108, 2, 0, 3),           # direct only, pinhole
+    ("s4096", 192, 108, 2, 50, 0),         # two hierarchy levels in use (128 groups, 16 L2 nodes)
+])
+def test_accel_equals_brute_force(gpu, scene_factory, name, w, h, spp, depth, flags):
+    """The hierarchy only decides WHICH spheres reach the cull + exact tests; hits, t and tie order come from the same
+    code as brute force, so the running sums and ray counters must be identical while fewer sphere tests are evaluated."""
+    rt = gpu
+    scene, _ = scene_factory(name)
+    cam = rt.scenes.default_camera(aspect=w / h)
+    r = _renderer(rt, scene, cam, w, h)
+    r.reset_stats()
+    r.render(spp, depth, flags)
+    a, sa = r.read_hdr_sum(), r.stats()
+    r.clear()
+    r.reset_stats()
+    r.render(spp, depth, flags | rt.RT_FLAG_ACCEL)
+    b, sb = r.read_hdr_sum(), r.stats()
+    assert np.array_equal(a, b)
+    assert (sa.paths, sa.closest_rays, sa.shadow_rays) == (sb.paths, sb.closest_rays, sb.shadow_rays)
+    if name != "small":                   # 40 spheres: one padded big group + two padded groups is not fewer tests than 40
+        assert sb.sphere_tests < sa.sphere_tests
+
+
+@pytest.mark.parametrize("name", ["d488", "s4096"])
+def test_accel_primary_hits_equal_brute_force(gpu, scene_factory, name):
+    """Brute force is pinned to the oracle by test_primary_hits_bit_exact; the hierarchy must reproduce its buffers."""
+    rt = gpu
+    w, h = 960, 540
+    scene, _ = scene_factory(name)
+    cam = rt.scenes.default_camera(aspect=w / h)
+    r = _renderer(rt, scene, cam, w, h)
+    for flags in (rt.RT_FLAG_JITTER_OFF | rt.RT_FLAG_LENS_OFF, 0):
+        ids0, mids0 = r.primary_hits(1, flags)
+        ids1, mids1 = r.primary_hits(1, flags | rt.RT_FLAG_ACCEL)
+        assert np.array_equal(ids0, ids1) and np.array_equal(mids0, mids1)
+
+
+def test_accel_far_origin_and_axis_aligned_rays(gpu):
+    """Stress the conservative slab test: camera far from the scene (large rounding in disc, large pad), a camera looking
+    straight down an axis (zero direction components), and a camera inside the small-sphere field."""
+    rt = gpu
+    w, h = 128, 96
+    scene = rt.scenes.scene_d488()
+    for origin, look in [((900.0, 40.0, -350.0), (0.0, 0.0, 0.0)), ((0.0, 30.0, 0.0), (0.0, 0.0, 0.0001)),
+                         ((0.3, 0.25, 0.4), (5.0, 0.2, 0.4)), ((12.0, 0.2, 0.0), (0.0, 0.2, 0.0))]:
+        cam = rt.Camera(origin, look, 25.0, w / h, 10.0, 0.0)
+        r = _renderer(rt, scene, cam, w, h)
+        r.render(2, 50, 0)
+        a = r.read_hdr_sum()
+        r.clear()
+        r.render(2, 50, rt.RT_FLAG_ACCEL)
+        b = r.read_hdr_sum()
+        assert np.array_equal(a, b, equal_nan=True), (origin, look)
+        f = rt.RT_FLAG_JITTER_OFF | rt.RT_FLAG_LENS_OFF
+        i0, m0 = r.primary_hits(1, f)
+        i1, m1 = r.primary_hits(1, f | rt.RT_FLAG_ACCEL)
+        assert np.array_equal(i0, i1) and np.array_equal(m0, m1)
+        r.close()
