@@ -4,7 +4,7 @@
 // (PPM / PFM / EXR) instead of a Direct2D window.  Host code only: every radiance value comes from the CUDA library.
 //
 //   spheres [--width W --height H] [--spp N] [--max-depth D] [--aperture A] [--focus F] [--exposure S]
-//           [--scene d488|s4096|small | --scene-file F] [--gpus G] [--seed K] [--jitter-off] [--lens-off]
+//           [--scene d488|s4096|small | --scene-file F | --ranlux-seed S] [--gpus G] [--seed K] [--jitter-off] [--lens-off] [--accel]
 //           [--frames-per-call K] [--out PREFIX] [--format ppm,pfm,exr] [--preview-every N]
 //           [--checkpoint F.exr] [--resume F.exr] [--dump-scene F] [--primary-hits F] [--selftest-sinks DIR] [--quiet]
 #include "../include/rt_b200.hpp"
@@ -14,7 +14,9 @@
 #include <chrono>
 #include <cstdlib>
 #include <cstring>
+#include <functional>
 #include <iostream>
+#include <random>
 #include <sstream>
 #include <unistd.h>
 
@@ -28,6 +30,7 @@ struct Settings {
     float verticalFov = 25.f, aperture = 0.4f, focus = -1.f /* <0: |origin - lookAt| */, exposure = -15.f;
     int spp = 16, gpus = 1, framesPerCall = 0, previewEvery = 0;
     uint32_t seed = 0, flags = 0;
+    long long ranluxSeed = -1;                   // >= 0: replay std::ranlux24_base(seed) as the reference's InitScene does
     std::string scene = "d488", sceneFile, out = "spheres", format = "ppm", checkpoint, resume, dumpScene, primaryHits, selftest;
     bool quiet = false;
 };
@@ -52,6 +55,12 @@ public:
     void OnInitialize() {
         InitCamera();
         if (!m_cfg.sceneFile.empty()) LoadSceneFile(m_cfg.sceneFile);
+        else if (m_cfg.ranluxSeed >= 0) {
+            // the reference's own generator (spheres-app.cpp:53-55) for a known std::random_device value: std::ranlux24_base's
+            // output is fixed by the C++ standard; MSVC's uniform_real_distribution<float>(0,1) maps one draw x to x * 2^-24
+            std::ranlux24_base generator(static_cast<uint32_t>(m_cfg.ranluxSeed));
+            InitScene(-11, 11, [&generator]() { return static_cast<float>(generator()) * (1.0f / 16777216.0f); }, -1);
+        }
         else if (m_cfg.scene == "d488") InitScene(-11, 11, 1, -1);          // spheres-app.cpp:64-66
         else if (m_cfg.scene == "s4096") InitScene(-32, 32, 2, 4092);       // N = 4096
         else if (m_cfg.scene == "small") InitScene(-3, 3, 3, -1);
@@ -68,9 +77,11 @@ public:
         m_exposure = m_cfg.exposure;
     }
 
-    void InitScene(int gridLo, int gridHi, uint64_t seed, int maxSmall) {   // spheres-app.cpp:51-130
+    void InitScene(int gridLo, int gridHi, uint64_t seed, int maxSmall) {
         SplitMix64 generator(seed);
-        auto uniformDist = [&generator]() { return generator.uniform(); };
+        InitScene(gridLo, gridHi, [&generator]() { return generator.uniform(); }, maxSmall);
+    }
+    void InitScene(int gridLo, int gridHi, const std::function<float()>& uniformDist, int maxSmall) {   // spheres-app.cpp:51-130
         // Floor
         m_textures.push_back(std::make_unique<CheckerTexture>(XMCOLOR{0.9f, 0.9f, 0.9f, 1.f}, XMCOLOR{0.2f, 0.3f, 0.1f, 1.f}, 2500.f));
         m_scene.push_back(std::make_unique<Sphere>(XMVectorSet(0, -1000, 0, 0), 1000.f, std::make_unique<DielectricOpaque>(m_textures.back().get(), XMVectorReplicate(16.f))));
@@ -289,10 +300,12 @@ int main(int argc, char** argv) {
             else if (a == "--exposure") s.exposure = std::stof(val());
             else if (a == "--scene") s.scene = val();
             else if (a == "--scene-file") s.sceneFile = val();
+            else if (a == "--ranlux-seed") s.ranluxSeed = std::stoll(val());
             else if (a == "--gpus") s.gpus = std::stoi(val());
             else if (a == "--seed") s.seed = static_cast<uint32_t>(std::stoul(val()));
             else if (a == "--jitter-off") s.flags |= RT_FLAG_JITTER_OFF;
             else if (a == "--lens-off") s.flags |= RT_FLAG_LENS_OFF;
+            else if (a == "--accel") s.flags |= RT_FLAG_ACCEL;
             else if (a == "--frames-per-call") s.framesPerCall = std::stoi(val());
             else if (a == "--preview-every") s.previewEvery = std::stoi(val());
             else if (a == "--out") s.out = val();

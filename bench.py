@@ -52,6 +52,9 @@ def parse_args():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--query", default="brute", choices=["brute", "accel"],
+                    help="closest-hit / occlusion query of the timed steps: brute force over every sphere (north_star, default) or the "
+                         "box hierarchy RT_FLAG_ACCEL (same bits); the default run also reports the other one under 'accel'")
     return ap.parse_args()
 
 
@@ -232,9 +235,11 @@ def run_b200(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    def step(i):
+    step_flags = rt.RT_FLAG_ACCEL if args.query == "accel" else 0
+
+    def step(i, flags=None):
         # global frame range of step i: [1 + i*world*spp_step, ...); each rank takes its disjoint share
-        sr.render(world * spp_step, depth, 0, first_sample=1 + i * world * spp_step, reduce=True)
+        sr.render(world * spp_step, depth, step_flags if flags is None else flags, first_sample=1 + i * world * spp_step, reduce=True)
 
     # ---- warm-up ----
     for i in range(args.warmup):
@@ -276,6 +281,27 @@ def run_b200(args):
         wsum = float(sr.hdr[..., 3].double().mean().item())
         assert abs(wsum - args.steps * world * spp_step) < 1e-3 * wsum, wsum
 
+    # ---- the other query mode on the same steps (informative; same bits, see tests/test_gpu_parity.py) ----
+    other = None
+    if args.query == "brute":
+        for i in range(2):
+            step(i, rt.RT_FLAG_ACCEL)
+        barrier()
+        sr.clear()
+        oev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+        for i in range(args.steps):
+            flush.fill_(i & 0xFF)
+            oev[i][0].record()
+            step(i, rt.RT_FLAG_ACCEL)
+            oev[i][1].record()
+        barrier()
+        oms = torch.tensor([sum(a.elapsed_time(b) for a, b in oev)], dtype=torch.float64, device=f"cuda:{local}")
+        if world > 1:
+            dist.all_reduce(oms, op=dist.ReduceOp.MAX)
+        other = {"query": "RT_FLAG_ACCEL box hierarchy (bit-identical results)", "value": paths / (float(oms.item()) * 1e-3),
+                 "unit": "path samples/s", "ms_per_step": float(oms.item()) / args.steps}
+        sr.clear()
+
     # ---- end to end through the public API with HOST buffers: scene arrays -> rt_scene_import/rt_set_scene (H2D),
     #      render (+ reduce), running-sum buffer -> pinned host memory (D2H) ----
     host_hdr = torch.empty((h, w, 4), dtype=torch.float32).pin_memory()
@@ -309,6 +335,7 @@ def run_b200(args):
             "config": {"workload": f"{args.workload} {desc}", "scene": scene_name, "n_spheres": int(len(flat.spheres)), "width": w,
                        "height": h, "max_depth": depth, "spp_per_step_per_gpu": spp_step, "config_spp": cfg_spp,
                        "partition": "disjoint sample ranges per GPU + ncclReduce(sum) to rank 0" if world > 1 else "single GPU",
+                       "query": "RT_FLAG_ACCEL box hierarchy in front of the cull + exact tests" if args.query == "accel" else "brute force over every sphere (north_star)",
                        "l2": "flushed between timed steps (256 MiB fill); scene lives in shared memory"},
             "rays_per_s": (float(counts[1].item()) + float(counts[2].item())) / total_s,
             "rays_per_path": (float(counts[1].item()) + float(counts[2].item())) / paths,
@@ -321,6 +348,9 @@ def run_b200(args):
                          "sphere_tests_per_s": tests / kern_s / world, "kernel_ms_per_step": 1e3 * kern_s / args.steps},
             "clocks": clocks, "wall_s": t_wall,
         }
+        if other is not None:
+            other["speedup_vs_value"] = other["value"] / value
+            line["accel"] = other
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(args.workload, args.cpu_seconds)
         _emit(line)

@@ -139,6 +139,7 @@ __device__ __forceinline__ QueryResult fused_query_accel(const AccelSmem& s, con
     ex.sA = s.sA; ex.sB = s.sB; ex.sR = s.sR; ex.o = o; ex.d = d; ex.L = L;
     ex.a = dot3(d, d);
     ex.aL = dot3(L, L);
+    ex.ra = rcp_refined(ex.a); ex.raL = rcp_refined(ex.aL);
     const uint32_t en_c = want_closest ? 0xffffffffu : 0u;
     uint32_t en_s = want_shadow ? 0xffffffffu : 0u;
     uint32_t* const gm = s.scratch;                                   // one byte per L2 node

@@ -145,7 +145,10 @@ __device__ __forceinline__ bool item_to_pixel(const RenderParams& p, u64 item, i
 // MODE: 0 = brute force with the conservative cull (default), 1 = brute force, every sphere through the exact test
 // (debug: proves the cull is result-neutral), 2 = RT_FLAG_ACCEL box hierarchy in front of the same cull (rt_bvh.cuh).
 enum { MODE_CULL = 0, MODE_NO_CULL = 1, MODE_ACCEL = 2 };
-#define RT_ACCEL_MAX_TPB 512   /* the hierarchy walk keeps two sets of slab constants live: 128 registers per thread */
+#ifndef RT_ACCEL_MAX_TPB
+#define RT_ACCEL_MAX_TPB 640
+#endif
+/* the hierarchy walk keeps two sets of slab constants live: 128 registers per thread */
 template <int MODE>
 __global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : RT_MAX_TPB) rt_render_kernel(const RenderParams p) {
     extern __shared__ __align__(16) unsigned char smem[];

@@ -44,6 +44,37 @@ class SplitMix64:
         return _f32((self.next_u64() >> 40) * (1.0 / 16777216.0))
 
 
+class Ranlux24Base:
+    """std::ranlux24_base = subtract_with_carry_engine<uint_fast32_t, 24, 10, 24> ([rand.predef]; its output is fixed by the
+    C++ standard, so this replays the reference's generator, spheres-app.cpp:54) + MSVC's uniform_real_distribution<float>
+    (0, 1): one engine draw x, u = float(x) / (float(max - min) + 1) = x * 2^-24 (VS2017 <random> _Nrand; FROM MEMORY of the
+    v141 toolset the reference pins, common-lib.vcxproj:23).  Given the seed std::random_device produced in a Windows run,
+    build_scene(prng=Ranlux24Base(seed)) regenerates that run's scene."""
+    W_MASK, R, S = (1 << 24) - 1, 24, 10
+
+    def __init__(self, seed: int = 19780503):
+        x = seed % 2147483563 if seed else 19780503            # linear_congruential_engine<uint_least32_t, 40014, 0, 2147483563>
+        if x == 0:
+            x = 1
+        self.x = []
+        for _ in range(self.R):
+            x = (x * 40014) % 2147483563
+            self.x.append(x & self.W_MASK)
+        self.carry = 1 if self.x[-1] == 0 else 0
+        self.p = 0
+
+    def next_u24(self) -> int:
+        y = self.x[(self.p + self.R - self.S) % self.R] - self.x[self.p] - self.carry
+        self.carry = 1 if y < 0 else 0
+        y &= self.W_MASK
+        self.x[self.p] = y
+        self.p = (self.p + 1) % self.R
+        return y
+
+    def uniform(self) -> np.float32:
+        return _f32(self.next_u24() * (1.0 / 16777216.0))
+
+
 def default_camera(aspect: float = K_BACKBUFFER_WIDTH / K_BACKBUFFER_HEIGHT, aperture: float = K_APERTURE) -> Camera:
     """SpheresApp::InitCamera, spheres-app.cpp:35-49: focus = |origin - lookAt| (float32 XMVector3Length)."""
     o = np.array([12.0, 2.0, -2.5], _f32)
@@ -54,10 +85,12 @@ def default_camera(aspect: float = K_BACKBUFFER_WIDTH / K_BACKBUFFER_HEIGHT, ape
                   float(focus), aperture)
 
 
-def build_scene(grid_lo: int = -11, grid_hi: int = 11, seed: int = 1, max_small: int | None = None) -> Scene:
+def build_scene(grid_lo: int = -11, grid_hi: int = 11, seed: int = 1, max_small: int | None = None, prng=None) -> Scene:
     """SpheresApp::InitScene, spheres-app.cpp:51-130, with a portable PRNG.  Draw order per cell (a outer,
-    b inner): chooseMat, cx, cz, then the material's own draws, left to right as written in the source."""
-    rng = SplitMix64(seed)
+    b inner): chooseMat, cx, cz, then the material's own draws, left to right as written in the source.
+    NB the colour draws `u() * u()` (spheres-app.cpp:74) are unsequenced operands in C++; MSVC x64 evaluates them left to
+    right, which is the order used here."""
+    rng = prng if prng is not None else SplitMix64(seed)
     u = rng.uniform
     scene = Scene()
     # Floor, :60-61
@@ -108,6 +141,11 @@ def scene_s4096() -> Scene:
 def scene_small(n_side: int = 3, seed: int = 3) -> Scene:
     """Tiny scene for fast parity tests: (2*n_side)^2 small spheres + ground + 3 large."""
     return build_scene(-n_side, n_side, seed=seed)
+
+
+def scene_ranlux(seed: int) -> Scene:
+    """The reference's own default scene for a given std::random_device seed (see Ranlux24Base)."""
+    return build_scene(-11, 11, prng=Ranlux24Base(seed))
 
 
 NAMED = {"d488": scene_d488, "s4096": scene_s4096, "small": scene_small}

@@ -211,3 +211,26 @@ def test_cli_two_gpus_equal_one(host, tmp_path):
     assert nb == spp and np.array_equal(a[..., 3], b[..., 3])           # every pixel got all 8 samples
     np.testing.assert_allclose(b[..., :3], a[..., :3], rtol=2e-6, atol=1e-9)   # reduction order differs, nothing else
     assert json.loads(r.stdout.strip().splitlines()[-1])["gpus"] == 2
+
+
+def test_ranlux24_base_known_answer(rt):
+    """[rand.predef]: the 10000th consecutive invocation of a default-constructed ranlux24_base produces 7937952."""
+    g = rt.scenes.Ranlux24Base()
+    for _ in range(9999):
+        g.next_u24()
+    assert g.next_u24() == 7937952
+
+
+@pytest.mark.parametrize("seed", [1, 123456789, 4000000000])
+def test_cpp_ranlux_scene_equals_python_replay(host, rt, tmp_path, seed):
+    """--ranlux-seed drives InitScene with std::ranlux24_base from <random> (the reference's generator, spheres-app.cpp:54);
+    the Python replay of the engine must record the same scene byte for byte."""
+    from cpuraytracer_b200 import _lib as L
+    path = tmp_path / "ranlux.rtsc"
+    run_cli(host[1], "--ranlux-seed", seed, "--dump-scene", path, "--spp", 0)
+    (sp, ma, te, li), sky_lum, sky_tex = read_rtsc(path, L)
+    flat = rt.scenes.scene_ranlux(seed).export()
+    assert len(sp) == 488
+    assert sp.tobytes() == flat.spheres.tobytes()
+    assert ma.tobytes() == flat.materials.tobytes()
+    assert te.tobytes() == flat.textures.tobytes()
