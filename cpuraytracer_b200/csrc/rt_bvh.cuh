@@ -17,8 +17,8 @@
 //   T  top             converged loop over the n2 L2 boxes                       -> bit mask m2 of touched L2 nodes
 //   M  middle          per lane: pop an L2 node, test its 8 group boxes          -> one byte per L2 node in shared memory
 //   G  groups          the big groups first (every lane, same addresses: broadcast LDS), then per lane: pop a touched group,
-//                      cull its 16 sphere pairs for both rays (pair order rotated by the lane id so that the quarter-warps'
-//                      LDS.128 hit 8 different bank groups)                      -> candidate-mask entries
+//                      cull its 16 sphere pairs for both rays (pair order XOR-swizzled by the lane id so that the
+//                      quarter-warps' LDS.128 hit 8 different bank groups)       -> candidate-mask entries
 //   E  exact           per lane: walk the entries, exact test per candidate
 #pragma once
 #include "rt_device.cuh"
@@ -63,7 +63,14 @@ __device__ __forceinline__ AccelSmem stage_accel(const AccelParams& a, unsigned 
     s.box = reinterpret_cast<const float*>(smem + a.off_box);
     s.top = reinterpret_cast<const float4*>(smem + a.off_top);
     s.scratch = reinterpret_cast<uint32_t*>(smem + a.blob_bytes) + threadIdx.x;
+    // the XOR-swizzled group loads (fused_query_accel, G) need the A and B sections on 256-byte boundaries
+    if ((static_cast<uint32_t>(__cvta_generic_to_shared(smem)) | static_cast<uint32_t>(a.off_B)) & 255u) __trap();
     return s;
+}
+
+__device__ __forceinline__ float4 lds128(uint32_t addr) {
+    float4 v; asm("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+    return v;
 }
 
 // Conservative discriminant signs of one sphere pair for both rays; as cull_pair() but (o-c).L is evaluated with three
@@ -143,7 +150,8 @@ __device__ __forceinline__ QueryResult fused_query_accel(const AccelSmem& s, con
     const uint32_t en_c = want_closest ? 0xffffffffu : 0u;
     uint32_t en_s = want_shadow ? 0xffffffffu : 0u;
     uint32_t* const gm = s.scratch;                                   // one byte per L2 node
-    uint32_t* const ent = s.scratch + a.gmask_words * lstride;        // entries: (mask, slot_base | shadow << 31)
+    uint32_t* const ent = s.scratch + a.gmask_words * lstride;        // entries: (mask, slot_base | 2 rot << 24 | shadow << 31)
+    const uint32_t sa32 = static_cast<uint32_t>(__cvta_generic_to_shared(s.sA)), sb32 = static_cast<uint32_t>(__cvta_generic_to_shared(s.sB));
 
     // ---- per-ray slab constants ----
     const float dcx = o.x - a.csx, dcy = o.y - a.csy, dcz = o.z - a.csz;
@@ -211,15 +219,18 @@ __device__ __forceinline__ QueryResult fused_query_accel(const AccelSmem& s, con
                 slot_base = (a.n_big_groups + curj * 8 + k) * 32; rot = rot_lane;
                 cnt.group_visits += (en_c & 1u) + (en_s & 1u);
             }
-            const float4* pa = s.sA + (slot_base >> 1);
-            const float4* pb = s.sB + (slot_base >> 1);
+            // pair q of this step is pair (q ^ rot) of the group: an XOR on a 256-byte aligned group is one LOP3 per address, and
+            // inside a quarter-warp (8 consecutive lanes) the 8 addresses fall into 8 different 16-byte bank groups.  The
+            // candidate masks stay in visiting order; E undoes the permutation per candidate (slot = base + (bit ^ 2 rot)).
+            const uint32_t pa = sa32 + static_cast<uint32_t>(slot_base) * 8u + (static_cast<uint32_t>(rot) << 4);
+            const uint32_t pb = sb32 + static_cast<uint32_t>(slot_base) * 8u + (static_cast<uint32_t>(rot) << 4);
             uint32_t mc = 0u, ms = 0u;
 #pragma unroll
-            for (int q = 0; q < 16; ++q) { const int qq = (q + rot) & 15; cull_pair2(cr, pa[qq], pb[qq], mc, ms); }
-            mc = __funnelshift_r(mc, mc, 2 * rot); ms = __funnelshift_r(ms, ms, 2 * rot);
+            for (int q = 0; q < 16; ++q) cull_pair2(cr, lds128(pa ^ (q << 4)), lds128(pb ^ (q << 4)), mc, ms);
             const uint32_t cc = ~mc & en_c, cs = ~ms & en_s;
-            if (cc) { ent[(2 * ne) * lstride] = cc; ent[(2 * ne + 1) * lstride] = static_cast<uint32_t>(slot_base); ++ne; }
-            if (cs) { ent[(2 * ne) * lstride] = cs; ent[(2 * ne + 1) * lstride] = static_cast<uint32_t>(slot_base) | 0x80000000u; ++ne; }
+            const uint32_t meta = static_cast<uint32_t>(slot_base) | (static_cast<uint32_t>(rot) << 25);
+            if (cc) { ent[(2 * ne) * lstride] = cc; ent[(2 * ne + 1) * lstride] = meta; ++ne; }
+            if (cs) { ent[(2 * ne) * lstride] = cs; ent[(2 * ne + 1) * lstride] = meta | 0x80000000u; ++ne; }
         }
         int e = 0; uint32_t cur = 0u, meta = 0u;
         for (;;) {
@@ -230,7 +241,7 @@ __device__ __forceinline__ QueryResult fused_query_accel(const AccelSmem& s, con
             }
             const int j = __clz(cur); cur &= ~(0x80000000u >> j);
             const bool sh = (meta >> 31) != 0u;
-            const int slot = static_cast<int>(meta & 0x7fffffffu) + j;
+            const int slot = static_cast<int>(meta & 0xffffffu) + (j ^ static_cast<int>((meta >> 24) & 0x7eu));
             float t;
             if (exact_candidate(ex, slot, sh, t)) {
                 if (sh) { res.occluded = true; en_s = 0u; cur = 0u; }

@@ -151,7 +151,7 @@ enum { MODE_CULL = 0, MODE_NO_CULL = 1, MODE_ACCEL = 2 };
 /* the hierarchy walk keeps two sets of slab constants live: 128 registers per thread */
 template <int MODE>
 __global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : RT_MAX_TPB) rt_render_kernel(const RenderParams p) {
-    extern __shared__ __align__(16) unsigned char smem[];
+    extern __shared__ __align__(256) unsigned char smem[];
     float4 *sA = nullptr, *sB = nullptr; float2* sC = nullptr; float* sR = nullptr; uint32_t* lists = nullptr;
     AccelSmem av{};
     if constexpr (MODE == MODE_ACCEL) {
@@ -326,7 +326,7 @@ __global__ void rt_resolve_kernel(const float4* __restrict__ hdr, uint32_t* __re
 // K6: primary-hit id buffers (jitter/lens per flags) for frame `first_sample`.
 template <int MODE>
 __global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : RT_MAX_TPB) rt_primary_kernel(const RenderParams p, int32_t* __restrict__ sphere_idx, int32_t* __restrict__ material_id) {
-    extern __shared__ __align__(16) unsigned char smem[];
+    extern __shared__ __align__(256) unsigned char smem[];
     float4 *sA = nullptr, *sB = nullptr; float2* sC = nullptr; float* sR = nullptr; uint32_t* lists = nullptr;
     AccelSmem av{};
     if constexpr (MODE == MODE_ACCEL) av = stage_accel(p.accel, smem);

@@ -25,7 +25,7 @@ enum { WF_WANT_CLOSEST = 1, WF_WANT_SHADOW = 2, WF_LIVE = 4, WF_DONE = 8, WF_OCC
 
 template <bool NO_CULL>
 __global__ void RT_RENDER_BOUNDS wf_intersect_kernel(const RenderParams p, const WfState s) {
-    extern __shared__ __align__(16) unsigned char smem[];
+    extern __shared__ __align__(256) unsigned char smem[];
     float4 *sA, *sB; float2* sC; float* sR; uint32_t* lists;
     stage_scene(p, sA, sB, sC, sR, lists, smem);
     const V3 Ldir = mk3(p.Lx, p.Ly, p.Lz);

@@ -320,3 +320,74 @@ def test_accel_far_origin_and_axis_aligned_rays(gpu):
         i1, m1 = r.primary_hits(1, f | rt.RT_FLAG_ACCEL)
         assert np.array_equal(i0, i1) and np.array_equal(m0, m1)
         r.close()
+
+
+def _random_scene(rt, rng, n, radius_spread, extent, with_ground):
+    """n spheres with log-uniform radii in a box of half-size `extent` (overlaps allowed), random materials."""
+    s = rt.Scene()
+    mats = [lambda: rt.DielectricOpaque(rt.ConstTexture(rt.XMCOLOR(*rng.uniform(0.1, 0.9, 3))), float(rng.uniform(0, 40))),
+            lambda: rt.Metal(rt.ConstTexture(rt.XMCOLOR(*rng.uniform(0.5, 1.0, 3))), 0.0),
+            lambda: rt.DielectricTransparent(float(rng.uniform(8, 40)), 1.5)]
+    if with_ground:
+        s.add(rt.Sphere((0.0, -1000.0, 0.0), 1000.0, rt.DielectricOpaque(rt.CheckerTexture(rt.XMCOLOR(0.9, 0.9, 0.9), rt.XMCOLOR(0.2, 0.3, 0.1), 2500.0), 16.0)))
+    for _ in range(n):
+        r = float(0.05 * radius_spread ** rng.uniform(0, 1))
+        c = rng.uniform(-extent, extent, 3)
+        if with_ground:
+            c[1] = abs(c[1]) * 0.2 + r
+        s.add(rt.Sphere(tuple(float(x) for x in c), r, mats[int(rng.integers(0, 3))]()))
+    s.set_sky(rt.Emissive(8000.0, rt.ConstTexture(rt.XMCOLOR(0.85, 0.91, 0.98))))
+    s.add_light(rt.DirectionalLight(tuple(float(x) for x in rng.uniform(-1, 1, 3) + np.array([0, 1.5, 0])), rt.XMCOLOR(1.0, 0.97, 0.88), 40000.0))
+    return s
+
+
+@pytest.mark.parametrize("seed,n,spread,extent,ground", [
+    (1, 1, 1.0, 1.0, False),        # a single sphere, no big group
+    (2, 33, 1.0, 3.0, False),       # equal radii: no big spheres at all, two groups
+    (3, 300, 3.0, 6.0, True),       # ground + mild radius spread
+    (4, 1000, 50.0, 10.0, True),    # radii over 1.7 decades: some spheres become "big", heavy overlap
+    (5, 2500, 8.0, 40.0, False),    # free-floating cloud, 10 L2 nodes
+    (6, 700, 20.0, 300.0, True),    # large coordinates (pad scales with distance)
+])
+def test_accel_equals_brute_force_on_random_scenes(gpu, seed, n, spread, extent, ground):
+    """Property test of the conservative slab test: on random sphere clouds and random cameras (inside and outside the
+    cloud) the hierarchy must reproduce brute force bit for bit -- running sums, ray counters and primary-hit buffers."""
+    rt = gpu
+    rng = np.random.default_rng(seed)
+    scene = _random_scene(rt, rng, n, spread, extent, ground)
+    w, h = 96, 64
+    for k in range(3):
+        origin = rng.uniform(-1.5 * extent, 1.5 * extent, 3)
+        if ground:
+            origin[1] = abs(origin[1]) * 0.3 + 0.05
+        look = rng.uniform(-0.3 * extent, 0.3 * extent, 3)
+        cam = rt.Camera(tuple(float(x) for x in origin), tuple(float(x) for x in look), 40.0, w / h, float(np.linalg.norm(origin - look)), 0.1 * k)
+        r = _renderer(rt, scene, cam, w, h)
+        r.reset_stats(); r.render(3, 50, 0)
+        a, sa = r.read_hdr_sum(), r.stats()
+        r.clear(); r.reset_stats(); r.render(3, 50, rt.RT_FLAG_ACCEL)
+        b, sb = r.read_hdr_sum(), r.stats()
+        assert np.array_equal(a, b, equal_nan=True), (seed, k)
+        assert (sa.paths, sa.closest_rays, sa.shadow_rays) == (sb.paths, sb.closest_rays, sb.shadow_rays)
+        i0, m0 = r.primary_hits(1, 0)
+        i1, m1 = r.primary_hits(1, rt.RT_FLAG_ACCEL)
+        assert np.array_equal(i0, i1) and np.array_equal(m0, m1)
+        r.close()
+
+
+def test_accel_empty_scene_and_limits(gpu):
+    rt = gpu
+    s = rt.Scene()
+    s.set_sky(rt.Emissive(8000.0, rt.ConstTexture(rt.XMCOLOR(0.85, 0.91, 0.98))))
+    r = _renderer(rt, s, rt.scenes.default_camera(), 64, 36)
+    r.render(2, 50, rt.RT_FLAG_ACCEL)
+    g = r.read_hdr_sum()
+    exp = (np.float32(8000.0) * (np.array([217, 232, 250], np.float32) * np.float32(1 / 255))) * np.float32(2.0 ** -15)
+    assert np.all(g[..., :3] == exp + exp) and np.all(g[..., 3] == 2)
+    ids, mids = r.primary_hits(1, rt.RT_FLAG_ACCEL)
+    assert np.all(ids == -1) and np.all(mids == rt.RT_MAT_SKY)
+    # flag combinations the library refuses loudly
+    with pytest.raises(rt.RtError):
+        r.render(1, 50, rt.RT_FLAG_ACCEL | rt.RT_FLAG_WAVEFRONT)
+    with pytest.raises(rt.RtError):
+        r.render(1, 50, rt.RT_FLAG_ACCEL | rt.RT_FLAG_DEBUG_NO_CULL)
