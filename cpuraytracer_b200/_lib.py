@@ -19,7 +19,7 @@ STATUS_NAMES = {0: "RT_OK", 1: "RT_ERR_INVALID_ARGUMENT", 2: "RT_ERR_CUDA", 3: "
                 4: "RT_ERR_NOT_READY", 5: "RT_ERR_UNSUPPORTED"}
 RT_MAT_OPAQUE, RT_MAT_METAL, RT_MAT_TRANSPARENT, RT_MAT_SKY = 0, 1, 2, 3
 RT_TEX_CONST, RT_TEX_CHECKER = 0, 1
-RT_FLAG_JITTER_OFF, RT_FLAG_LENS_OFF, RT_FLAG_WAVEFRONT, RT_FLAG_ACCEL, RT_FLAG_DEBUG_NO_CULL = 1, 2, 4, 8, 0x100
+RT_FLAG_JITTER_OFF, RT_FLAG_LENS_OFF, RT_FLAG_WAVEFRONT, RT_FLAG_ACCEL, RT_FLAG_HALTON, RT_FLAG_DEBUG_NO_CULL = 1, 2, 4, 8, 16, 0x100
 
 # flat scene description v1 (byte-identical to the structs in include/rt_b200.h)
 SPHERE_DTYPE = np.dtype([("cx", "<f4"), ("cy", "<f4"), ("cz", "<f4"), ("radius", "<f4"), ("material", "<i4")])
@@ -81,6 +81,7 @@ SYMBOLS = [
     ("rt_camera_basis_of", C.c_int, [C.POINTER(CameraParams), C.POINTER(CameraBasis)]),
     ("rt_set_exposure", C.c_int, [_P, C.c_float]),
     ("rt_set_seed", C.c_int, [_P, C.c_uint32]),
+    ("rt_sampler_reset", C.c_int, [_P]),
     ("rt_set_chunk_spp", C.c_int, [_P, C.c_int]),
     ("rt_framebuffer_resize", C.c_int, [_P, C.c_int, C.c_int]),
     ("rt_framebuffer_clear", C.c_int, [_P]),

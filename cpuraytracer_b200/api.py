@@ -275,6 +275,10 @@ class Renderer:
     def set_seed(self, seed: int) -> None:
         L.check(self._lib.rt_set_seed(self._h, seed))
 
+    def reset_sampler(self) -> None:
+        """RT_FLAG_HALTON: every material's Halton indices back to 0 (as after InitScene)."""
+        L.check(self._lib.rt_sampler_reset(self._h))
+
     def set_chunk_spp(self, chunk: int) -> None:
         L.check(self._lib.rt_set_chunk_spp(self._h, chunk))
 

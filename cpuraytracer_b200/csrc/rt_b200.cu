@@ -244,6 +244,7 @@ struct rt_context {
     int render_blocks_per_sm = 0, tpb = 256;
     // RT_FLAG_ACCEL: shared-memory image of the box hierarchy (rt_bvh.cuh), built by rt_set_scene
     uint4* accel_blob = nullptr; bool accel_ok = false; std::string accel_why;
+    u64* sampler = nullptr; size_t n_sampler = 0;   // RT_FLAG_HALTON: per-material-instance Halton indices (material.h:34,50-51,67)
     int accel_tpb = 0, accel_bps = 0;
 
     float4* hdr() const { return hdr_ext ? hdr_ext : hdr_own; }
@@ -467,7 +468,7 @@ void rt_context_destroy(rt_context* c) {
     cudaStreamSynchronize(c->stream);
     ev_collect(c);
     for (auto& e : c->pool) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
-    cudaFree(c->geom); cudaFree(c->wf_block); cudaFree(c->wf_live); cudaFree(c->accel_blob);
+    cudaFree(c->geom); cudaFree(c->wf_block); cudaFree(c->wf_live); cudaFree(c->accel_blob); cudaFree(c->sampler);
     cudaFree(c->cullA); cudaFree(c->cullB); cudaFree(c->cullC); cudaFree(c->radius); cudaFree(c->mats);
     cudaFree(c->hdr_own); cudaFree(c->ldr); cudaFree(c->ids); cudaFree(c->mids); cudaFree(c->partial);
     cudaFree(c->jitter); cudaFree(c->lens); cudaFree(c->counters);
@@ -491,6 +492,13 @@ int rt_synchronize(rt_context* c) {
 }
 int rt_set_exposure(rt_context* c, float stops) { if (!c) return fail(RT_ERR_INVALID_ARGUMENT, "rt_set_exposure: ctx is NULL"); c->exposure_stops = stops; return RT_OK; }
 int rt_set_seed(rt_context* c, uint32_t seed) { if (!c) return fail(RT_ERR_INVALID_ARGUMENT, "rt_set_seed: ctx is NULL"); c->seed = seed; return RT_OK; }
+int rt_sampler_reset(rt_context* c) {
+    if (!c) return fail(RT_ERR_INVALID_ARGUMENT, "rt_sampler_reset: ctx is NULL");
+    if (!c->sampler) return fail(RT_ERR_NOT_READY, "rt_sampler_reset: no scene set");
+    if (int r = ctx_use(c)) return r;
+    RT_CUDA(cudaMemsetAsync(c->sampler, 0, c->n_sampler * sizeof(u64), c->stream));
+    return RT_OK;
+}
 int rt_set_chunk_spp(rt_context* c, int chunk) {
     if (!c || chunk < 0) return fail(RT_ERR_INVALID_ARGUMENT, "rt_set_chunk_spp: bad argument");
     c->chunk_spp = chunk; return RT_OK;
@@ -533,7 +541,7 @@ int rt_set_scene(rt_context* c, const rt_scene* s) {
     }
     for (int i = 0; i < n; ++i) {
         const rt_material_desc& m = s->materials[s->spheres[i].material];
-        rt::DevMat dm{}; dm.kind = m.kind; dm.smoothness = m.smoothness; dm.ior = m.ior;
+        rt::DevMat dm{}; dm.kind = m.kind; dm.smoothness = m.smoothness; dm.ior = m.ior; dm.mat_index = s->spheres[i].material;
         if (m.texture >= 0) {
             const rt_texture_desc& t = s->textures[m.texture];
             dm.tex_kind = t.kind; dm.tiling = t.tiling;
@@ -546,6 +554,9 @@ int rt_set_scene(rt_context* c, const rt_scene* s) {
     if (int r = dev_realloc(c->cullC, np)) return r;
     if (int r = dev_realloc(c->radius, n_pad)) return r;
     if (int r = dev_realloc(c->mats, M.size())) return r;
+    c->n_sampler = 2 * std::max<size_t>(1, s->materials.size());
+    if (int r = dev_realloc(c->sampler, c->n_sampler)) return r;
+    RT_CUDA(cudaMemsetAsync(c->sampler, 0, c->n_sampler * sizeof(u64), c->stream));      // the reference's indices start at 0 with the scene
     std::vector<float4> G(std::max(n, 1), make_float4(0.f, 0.f, 0.f, 1.f));
     for (int i = 0; i < n; ++i) G[i] = make_float4(s->spheres[i].cx, s->spheres[i].cy, s->spheres[i].cz, s->spheres[i].radius);
     if (int r = dev_realloc(c->geom, G.size())) return r;
@@ -558,6 +569,7 @@ int rt_set_scene(rt_context* c, const rt_scene* s) {
     RT_CUDA(cudaStreamSynchronize(c->stream));
     rt::RenderParams& b = c->base;
     b.cullA = c->cullA; b.cullB = c->cullB; b.cullC = c->cullC; b.radius = c->radius; b.mats = c->mats; b.sphere_geom = c->geom;
+    b.sampler = c->sampler;
     b.n_spheres = n; b.n_pairs_pad = np; b.n_groups = n_pad / 32; b.n_lights = has_light ? 1 : 0;
     b.Lx = b.Ly = b.Lz = 0.f; b.lcx = b.lcy = b.lcz = 0.f;
     if (has_light) {
@@ -574,6 +586,7 @@ int rt_set_scene(rt_context* c, const rt_scene* s) {
     const int optin = static_cast<int>(c->prop.sharedMemPerBlockOptin);
     RT_CUDA(cudaFuncSetAttribute(rt::rt_render_kernel<rt::MODE_CULL>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
     RT_CUDA(cudaFuncSetAttribute(rt::rt_render_kernel<rt::MODE_NO_CULL>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
+    RT_CUDA((cudaFuncSetAttribute(rt::rt_render_kernel<rt::MODE_CULL, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin)));
     RT_CUDA(cudaFuncSetAttribute(rt::rt_primary_kernel<rt::MODE_CULL>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
     RT_CUDA(cudaFuncSetAttribute(rt::rt_primary_kernel<rt::MODE_NO_CULL>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
     RT_CUDA(cudaFuncSetAttribute(rt::wf_intersect_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
@@ -711,7 +724,8 @@ int rt_render(rt_context* c, uint64_t first_sample, int spp, int max_depth, uint
     if (!c) return fail(RT_ERR_INVALID_ARGUMENT, "rt_render: ctx is NULL");
     if (!c->scene_set || !c->camera_set || !c->hdr()) return fail(RT_ERR_NOT_READY, "rt_render: scene, camera and framebuffer must be set first");
     if (first_sample < 1 || spp < 0 || max_depth < 0) return fail(RT_ERR_INVALID_ARGUMENT, "rt_render: first_sample >= 1, spp >= 0, max_depth >= 0 required");
-    if (flags & ~(RT_FLAG_JITTER_OFF | RT_FLAG_LENS_OFF | RT_FLAG_WAVEFRONT | RT_FLAG_ACCEL | RT_FLAG_DEBUG_NO_CULL_)) return fail(RT_ERR_INVALID_ARGUMENT, "rt_render: unknown flag bits 0x%x", flags);
+    if (flags & ~(RT_FLAG_JITTER_OFF | RT_FLAG_LENS_OFF | RT_FLAG_WAVEFRONT | RT_FLAG_ACCEL | RT_FLAG_HALTON | RT_FLAG_DEBUG_NO_CULL_)) return fail(RT_ERR_INVALID_ARGUMENT, "rt_render: unknown flag bits 0x%x", flags);
+    if ((flags & RT_FLAG_HALTON) && (flags & (RT_FLAG_WAVEFRONT | RT_FLAG_ACCEL | RT_FLAG_DEBUG_NO_CULL_))) return fail(RT_ERR_INVALID_ARGUMENT, "rt_render: RT_FLAG_HALTON runs on the default brute-force megakernel only");
     if ((flags & RT_FLAG_ACCEL) && (flags & (RT_FLAG_WAVEFRONT | RT_FLAG_DEBUG_NO_CULL_))) return fail(RT_ERR_INVALID_ARGUMENT, "rt_render: RT_FLAG_ACCEL cannot be combined with the wavefront layout or the no-cull debug mode");
     if ((flags & RT_FLAG_ACCEL) && !c->accel_ok) return fail(RT_ERR_UNSUPPORTED, "rt_render: RT_FLAG_ACCEL unavailable for this scene: %s", c->accel_why.c_str());
     if ((flags & RT_FLAG_WAVEFRONT) && max_depth >= (1 << 22)) return fail(RT_ERR_INVALID_ARGUMENT, "rt_render: the wavefront layout packs the depth into 23 bits");
@@ -741,6 +755,9 @@ int rt_render(rt_context* c, uint64_t first_sample, int spp, int max_depth, uint
     if (flags & RT_FLAG_WAVEFRONT) { if (int r = render_wavefront(c, p, flags)) return r; }
     else if (flags & RT_FLAG_ACCEL) {
         rt::rt_render_kernel<rt::MODE_ACCEL><<<c->prop.multiProcessorCount * c->accel_bps, c->accel_tpb, accel_cta_smem_bytes(p.accel, c->accel_tpb), c->stream>>>(p);
+        ++c->launches;
+    } else if (flags & RT_FLAG_HALTON) {
+        rt::rt_render_kernel<rt::MODE_CULL, true><<<grid, c->tpb, smem, c->stream>>>(p);
         ++c->launches;
     } else {
         if (flags & RT_FLAG_DEBUG_NO_CULL_) rt::rt_render_kernel<rt::MODE_NO_CULL><<<grid, c->tpb, smem, c->stream>>>(p);

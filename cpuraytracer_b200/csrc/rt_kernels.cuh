@@ -38,12 +38,14 @@ struct RenderParams {
                                  // [5] sphere tests evaluated for rays that asked for them (both query modes)
     AccelParams accel;           // RT_FLAG_ACCEL: box hierarchy image (rt_bvh.cuh)
     float iLx, iLy, iLz;         // safe_inv of the light direction (slab test of the shadow ray)
+    u64* sampler;                // RT_FLAG_HALTON: [n_materials][2] = (m_reflectionProbabilitySampleIndex, m_sampleIndex), material.h:34,50-51,67
 };
 
 #define RT_FLAG_JITTER_OFF_ 1u
 #define RT_FLAG_LENS_OFF_ 2u
 #define RT_FLAG_WAVEFRONT_ 4u
 #define RT_FLAG_ACCEL_ 8u
+#define RT_FLAG_HALTON_ 16u
 #define RT_FLAG_DEBUG_NO_CULL_ 0x100u
 
 enum LaneState { ST_NEED_ITEM = 0, ST_NEW_PATH = 1, ST_IN_PATH = 2, ST_DONE = 3 };
@@ -130,6 +132,29 @@ __device__ __forceinline__ bool scatter(const DevMat& m, V3 d, V3 pos, V3 n, flo
     return true;
 }
 
+// RT_FLAG_HALTON: the reference's sampler -- one post-incremented Halton index per material instance and purpose
+// (material.cpp:29,44,82,151), drawn in the order and under the conditions Scatter draws them.  The counters live in global
+// memory and are shared by every path, exactly as the reference's std::atomic members are shared by its worker threads, so
+// (like the reference) the image is reproducible only when paths run one after the other (a 1x1 framebuffer here).
+__device__ __forceinline__ void draw_halton(const DevMat& m, u64* sampler, V3 d, V3 n, float& xi, float& u1, float& u2) {
+    u64* c = sampler + 2 * m.mat_index;
+    xi = 0.f; u1 = 0.f; u2 = 0.f;
+    if (m.kind == 0) {
+        const float ndv = dot3(neg3(d), n);
+        if (!(ndv > 0.f)) return;                                              // :22
+        xi = halton_sample(atomicAdd(&c[0], 1ull), 3);                         // :29
+        if (!(schlick(0.04f, saturate1(ndv)) > xi)) {                          // :30
+            const u64 k = atomicAdd(&c[1], 1ull);                              // :44
+            u1 = halton_sample(k, 5); u2 = halton_sample(k, 7);
+        }
+    } else if (m.kind == 1) {
+        if (!(dot3(neg3(d), n) > 0.f)) return;                                 // :74
+        xi = halton_sample(atomicAdd(&c[0], 1ull), 3);                         // :82
+    } else {
+        xi = halton_sample(atomicAdd(&c[1], 1ull), 7);                         // :151
+    }
+}
+
 // Maps a linear work index to (chunk, pixel).  Pixels are enumerated in 8x4 tiles so the 32 lanes of a warp
 // start on a compact screen tile (coherent primary rays); chunks are the outer loop.
 __device__ __forceinline__ bool item_to_pixel(const RenderParams& p, u64 item, int& chunk, int& px, int& py) {
@@ -149,7 +174,7 @@ enum { MODE_CULL = 0, MODE_NO_CULL = 1, MODE_ACCEL = 2 };
 #define RT_ACCEL_MAX_TPB 640
 #endif
 /* the hierarchy walk keeps two sets of slab constants live: 128 registers per thread */
-template <int MODE>
+template <int MODE, bool HALTON = false>
 __global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : RT_MAX_TPB) rt_render_kernel(const RenderParams p) {
     extern __shared__ __align__(256) unsigned char smem[];
     float4 *sA = nullptr, *sB = nullptr; float2* sC = nullptr; float* sR = nullptr; uint32_t* lists = nullptr;
@@ -240,9 +265,10 @@ __global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : RT_MAX
                     const bool cont = depth < p.max_depth;                               // spheres-app.cpp:247
                     V3 atten = mk3(0.f, 0.f, 0.f), nd = d;
                     bool scattered = false;
-                    if (cont) {
+                    if (cont || HALTON) {                                                // the reference scatters before it tests the depth (:246-247)
                         float xi, u1, u2;
-                        rng_counter(static_cast<uint32_t>(pix), p.first_sample + static_cast<u64>(s_cur), static_cast<uint32_t>(depth), p.seed, xi, u1, u2);
+                        if constexpr (HALTON) draw_halton(m, p.sampler, d, n, xi, u1, u2);
+                        else rng_counter(static_cast<uint32_t>(pix), p.first_sample + static_cast<u64>(s_cur), static_cast<uint32_t>(depth), p.seed, xi, u1, u2);
                         scattered = scatter(m, d, pos, n, tu, tv, xi, u1, u2, atten, nd);      // :246
                     }
                     if (has_light) {                                                     // :250

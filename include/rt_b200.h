@@ -65,6 +65,12 @@ enum { RT_FLAG_JITTER_OFF = 1u,   /* jitterOffset = 0 (spheres-app.cpp:140)     
        RT_FLAG_ACCEL = 8u };      /* closest-hit / occlusion queries go through a bounding-box hierarchy (what BvhNode::Intersect,
                                      ray-tracing.cpp:174-214, does in the reference) before the same cull + exact tests; returns the
                                      same bits as the default brute-force query, only faster on large scenes */
+/* RT_FLAG_HALTON (16u): draw the scatter randoms from the reference's sampler -- one post-incremented Halton index per material
+ * instance (m_reflectionProbabilitySampleIndex / m_sampleIndex, material.h:34,50-51,67; material.cpp:29,44,82,151) -- instead
+ * of the stateless counter RNG.  The indices are shared by all paths (device atomics), start at 0 in rt_set_scene and persist
+ * across rt_render calls, as the reference's members do; like the reference, the result is reproducible only when paths run
+ * one after another (1x1 framebuffer), and statistically equivalent otherwise.  Brute-force megakernel only. */
+enum { RT_FLAG_HALTON = 16u };
 
 typedef struct rt_stats {
     uint64_t paths;            /* path samples traced since the last rt_stats_reset            */
@@ -124,6 +130,7 @@ RT_API int  rt_set_camera(rt_context* ctx, const rt_camera_params* cam);     /* 
 RT_API int  rt_camera_basis_of(const rt_camera_params* cam, rt_camera_basis* out);   /* Camera::Camera, camera.cpp:3-28 (host only) */
 RT_API int  rt_set_exposure(rt_context* ctx, float stops);                   /* m_exposure, default -15: spheres-app.cpp:48 */
 RT_API int  rt_set_seed(rt_context* ctx, uint32_t seed);                     /* counter-RNG stream selector, default 0 */
+RT_API int  rt_sampler_reset(rt_context* ctx);                                /* RT_FLAG_HALTON: set every material's Halton indices back to 0 */
 RT_API int  rt_set_chunk_spp(rt_context* ctx, int chunk_spp);                /* 0 = auto; samples per work item (load balance) */
 /* InitBuffers (app.cpp:112-119): allocate W*H float4 running-sum + BGRA8 buffers, zero-filled. */
 RT_API int  rt_framebuffer_resize(rt_context* ctx, int width, int height);
