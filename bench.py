@@ -281,6 +281,27 @@ def run_b200(args):
         wsum = float(sr.hdr[..., 3].double().mean().item())
         assert abs(wsum - args.steps * world * spp_step) < 1e-3 * wsum, wsum
 
+    # ---- K5, the only HBM-bound kernel of the path (north_star: "HBM GB/s is reported only for the accumulation pass"):
+    #      resolve = 16 B read + 4 B write per pixel, L2 flushed before every launch, CUDA events inside rt_resolve_ldr ----
+    accumulation = None
+    if rank == 0:
+        r.reset_stats()
+        n_res = 10
+        for i in range(n_res):
+            flush.fill_(i & 0xFF)
+            r.resolve_ldr(sample_count=args.steps * world * spp_step, copy=False)
+        rs = r.stats()
+        res_s = rs.resolve_ms * 1e-3 / n_res
+        hbm_peak = 6550.7
+        try:
+            hbm_peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
+        except Exception:
+            pass
+        accumulation = {"kernel": "rt_resolve_kernel (mean, ACES, gamma, BGRA8)", "bytes_per_launch": 20 * n_pix, "us_per_launch": res_s * 1e6,
+                        "achieved_gbs": 20 * n_pix / res_s / 1e9, "peak_gbs": hbm_peak, "frac": 20 * n_pix / res_s / 1e9 / hbm_peak,
+                        "note": "peak = MEASURED_PEAKS.json hbm_gbs (driver-measured copy bandwidth)"}
+        r.reset_stats()
+
     # ---- the other query mode on the same steps (informative; same bits, see tests/test_gpu_parity.py) ----
     other = None
     if args.query == "brute":
@@ -351,6 +372,8 @@ def run_b200(args):
         if other is not None:
             other["speedup_vs_value"] = other["value"] / value
             line["accel"] = other
+        if accumulation is not None:
+            line["accumulation"] = accumulation
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(args.workload, args.cpu_seconds)
         _emit(line)

@@ -326,26 +326,44 @@ __global__ void rt_combine_kernel(float4* __restrict__ hdr, const float4* __rest
 }
 
 // K5 resolve, spheres-app.cpp:186-214.  16 B read + 4 B write per pixel (HBM-bound).
-__device__ __forceinline__ uint32_t store_color_channel(float x) {          // XMStoreColor: saturate, *255, round-to-nearest-even
-    float v = fminf(fmaxf(x, 0.0f), 1.0f);
+// powf(x, 1/2.2) followed by XMStoreColor's x255 + round-to-nearest-even, for x in [0,1].  The SFU form ex2(g * lg2(x)) is
+// within ~1e-6 relative of powf (MUFU.LG2 / MUFU.EX2: <= 2^-21 absolute on the exponent, 2^-22 relative on the result), i.e.
+// within 3e-4 of powf * 255; the rounded code can therefore differ only when the scaled value sits within 2e-3 of a
+// half-integer, and exactly those values (0.4 % of the channels) are recomputed with powf.  Output == the powf-only kernel.
+__device__ __forceinline__ uint32_t gamma_store_channel(float x, float inv_gamma) {
+    if (!(x > 0.0f)) return 0u;                                              // powf(0, g) = 0 (x is already saturated: never negative / NaN-free)
+    float lg, v;
+    asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(lg) : "f"(x));                   // a denormal x is flushed: its power scales to code 0 either way
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(v) : "f"(inv_gamma * lg));
     v = v * 255.0f;
-    return static_cast<uint32_t>(__float2int_rn(v));
+    if (fabsf(fabsf(v - rintf(v)) - 0.5f) < 2e-3f) v = powf(x, inv_gamma) * 255.0f;   // spheres-app.cpp:208 as written
+    v = fminf(v, 255.0f);
+    return static_cast<uint32_t>(__float2int_rn(v));                         // :211 XMStoreColor
 }
-__global__ void rt_resolve_kernel(const float4* __restrict__ hdr, uint32_t* __restrict__ ldr, float n, size_t n_pixels) {
+__device__ __forceinline__ uint32_t resolve_pixel(const float4 h, float n, float rn) {
     const float a = 2.51f, b = 0.03f, c = 2.43f, dd = 0.59f, e = 0.14f;
     const float inv_gamma = 1 / 2.2f;
-    for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n_pixels; i += static_cast<size_t>(gridDim.x) * blockDim.x) {
-        const float4 h = hdr[i];
-        float ch[3] = {h.x, h.y, h.z};
-        uint32_t out[3];
+    const float ch[3] = {h.x, h.y, h.z};
+    uint32_t out[3];
 #pragma unroll
-        for (int k = 0; k < 3; ++k) {
-            float x = ch[k] / n;                                             // :201
-            x = saturate1((x * (a * x + b)) / (x * (c * x + dd) + e));      // :205
-            x = powf(x, inv_gamma);                                          // :208
-            out[k] = store_color_channel(x);                                 // :211
-        }
-        ldr[i] = 0xFF000000u | (out[0] << 16) | (out[1] << 8) | out[2];
+    for (int k = 0; k < 3; ++k) {
+        float x = div_by(ch[k], n, rn);                                      // :201
+        x = saturate1(div_rn(x * (a * x + b), x * (c * x + dd) + e));        // :205 (denominator >= 0.14)
+        out[k] = gamma_store_channel(x, inv_gamma);                          // :208, :211
+    }
+    return 0xFF000000u | (out[0] << 16) | (out[1] << 8) | out[2];
+}
+// Four pixels per thread and iteration, loads issued before any arithmetic (4 x 16 B in flight per thread), streaming
+// cache hints on both sides (every byte is touched once).
+__global__ void __launch_bounds__(256) rt_resolve_kernel(const float4* __restrict__ hdr, uint32_t* __restrict__ ldr, float n, size_t n_pixels) {
+    const float rn = rcp_refined(n);
+    const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+    for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n_pixels; i += 4 * stride) {
+        float4 h[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) { const size_t j = i + u * stride; if (j < n_pixels) h[u] = __ldcs(&hdr[j]); }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) { const size_t j = i + u * stride; if (j < n_pixels) __stcs(&ldr[j], resolve_pixel(h[u], n, rn)); }
     }
 }
 
