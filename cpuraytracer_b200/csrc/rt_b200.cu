@@ -244,6 +244,8 @@ struct rt_context {
     int render_blocks_per_sm = 0, tpb = 256;
     // RT_FLAG_ACCEL: shared-memory image of the box hierarchy (rt_bvh.cuh), built by rt_set_scene
     uint4* accel_blob = nullptr; bool accel_ok = false; std::string accel_why;
+    struct ExtraLight { float L[3], lc[3], iL[3]; float2* cullC; };
+    std::vector<ExtraLight> extra_lights; float2* extra_cullC = nullptr;   // lights 1.. (one additional launch each, see rt_render)
     u64* sampler = nullptr; size_t n_sampler = 0;   // RT_FLAG_HALTON: per-material-instance Halton indices (material.h:34,50-51,67)
     int accel_tpb = 0, accel_bps = 0;
 
@@ -468,7 +470,7 @@ void rt_context_destroy(rt_context* c) {
     cudaStreamSynchronize(c->stream);
     ev_collect(c);
     for (auto& e : c->pool) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
-    cudaFree(c->geom); cudaFree(c->wf_block); cudaFree(c->wf_live); cudaFree(c->accel_blob); cudaFree(c->sampler);
+    cudaFree(c->geom); cudaFree(c->wf_block); cudaFree(c->wf_live); cudaFree(c->accel_blob); cudaFree(c->sampler); cudaFree(c->extra_cullC);
     cudaFree(c->cullA); cudaFree(c->cullB); cudaFree(c->cullC); cudaFree(c->radius); cudaFree(c->mats);
     cudaFree(c->hdr_own); cudaFree(c->ldr); cudaFree(c->ids); cudaFree(c->mids); cudaFree(c->partial);
     cudaFree(c->jitter); cudaFree(c->lens); cudaFree(c->counters);
@@ -507,7 +509,6 @@ int rt_set_chunk_spp(rt_context* c, int chunk) {
 int rt_set_scene(rt_context* c, const rt_scene* s) {
     if (!c || !s) return fail(RT_ERR_INVALID_ARGUMENT, "rt_set_scene: NULL argument");
     if (s->sky_texture < 0) return fail(RT_ERR_NOT_READY, "rt_set_scene: the scene has no sky (rt_scene_set_sky)");
-    if (s->lights.size() > 1) return fail(RT_ERR_UNSUPPORTED, "rt_set_scene: %zu lights given; this build fuses exactly one shadow query per vertex (0 or 1 directional light)", s->lights.size());
     if (int r = ctx_use(c)) return r;
     const int n = static_cast<int>(s->spheres.size());
     const int n_pad = std::max(32, (n + 31) / 32 * 32);
@@ -577,6 +578,32 @@ int rt_set_scene(rt_context* c, const rt_scene* s) {
         b.Lx = Ln.x; b.Ly = Ln.y; b.Lz = Ln.z;
         b.lcx = l.luminance * l.color[0]; b.lcy = l.luminance * l.color[1]; b.lcz = l.luminance * l.color[2];   // light.cpp:27
     }
+    // Lights 1..: Material::Shade sums over m_lights (material.cpp:4-13).  Radiance is linear in the emitters and the counter
+    // RNG makes the paths independent of the lights, so light k > 0 is one more launch over the SAME paths with only that
+    // light switched on and the sky switched off, accumulated into the same running sum (rt_render).
+    c->extra_lights.clear();
+    if (s->lights.size() > 1) {
+        const size_t ne = s->lights.size() - 1;
+        if (int r = dev_realloc(c->extra_cullC, ne * np)) return r;
+        std::vector<float2> CE(ne * np);
+        for (size_t k = 1; k < s->lights.size(); ++k) {
+            const rt_light_desc& l = s->lights[k];
+            const host::V3 Lk = host::normalize3({l.dir[0], l.dir[1], l.dir[2]});
+            rt_context::ExtraLight e{};
+            e.L[0] = Lk.x; e.L[1] = Lk.y; e.L[2] = Lk.z;
+            for (int q = 0; q < 3; ++q) e.lc[q] = l.luminance * l.color[q];
+            e.cullC = c->extra_cullC + (k - 1) * np;
+            for (int p = 0; p < np; ++p) {
+                float v[2] = {0.f, 0.f};
+                for (int h = 0; h < 2; ++h) { const int i = 2 * p + h; if (i < n) { const rt_sphere_desc& sp = s->spheres[i];
+                    v[h] = static_cast<float>(-(sp.cx * static_cast<double>(Lk.x) + sp.cy * static_cast<double>(Lk.y) + sp.cz * static_cast<double>(Lk.z))); } }
+                CE[(k - 1) * np + p] = make_float2(v[0], v[1]);
+            }
+            c->extra_lights.push_back(e);
+        }
+        RT_CUDA(cudaMemcpyAsync(c->extra_cullC, CE.data(), CE.size() * sizeof(float2), cudaMemcpyHostToDevice, c->stream));
+        RT_CUDA(cudaStreamSynchronize(c->stream));
+    }
     const rt_texture_desc& sky = s->textures[s->sky_texture];              // Emissive::Emit at uv = (0,0): material.cpp:172-175
     const float* sc = sky.c0;                                             // checker at (0,0): u%2 == v%2 -> colour 0
     b.skyx = s->sky_luminance * sc[0]; b.skyy = s->sky_luminance * sc[1]; b.skyz = s->sky_luminance * sc[2];
@@ -606,6 +633,8 @@ int rt_set_scene(rt_context* c, const rt_scene* s) {
     if (c->wf_bps < 1) c->wf_bps = 1;
     auto safe_inv = [](float d) { const float dd = std::fabs(d) < 1e-18f ? std::copysign(1e-18f, d) : d; return 1.0f / dd; };   // rt_bvh.cuh safe_inv
     b.iLx = safe_inv(b.Lx); b.iLy = safe_inv(b.Ly); b.iLz = safe_inv(b.Lz);
+    for (auto& e : c->extra_lights) for (int q = 0; q < 3; ++q) e.iL[q] = safe_inv(e.L[q]);
+    b.primary_pass = 1;
     return build_accel(c, s);
 }
 
@@ -748,25 +777,36 @@ int rt_render(rt_context* c, uint64_t first_sample, int spp, int max_depth, uint
         }
         p.partial = c->partial;
     }
-    RT_CUDA(cudaMemsetAsync(c->counters, 0, sizeof(u64), c->stream));
     const size_t smem = cta_smem_bytes(c->n_pad, c->tpb);
     const int grid = c->prop.multiProcessorCount * c->render_blocks_per_sm;
+    if (!c->extra_lights.empty() && (flags & (RT_FLAG_WAVEFRONT | RT_FLAG_HALTON)))
+        return fail(RT_ERR_UNSUPPORTED, "rt_render: scenes with more than one light run on the megakernel with the counter RNG only (one launch per light over the same paths)");
     EventPair ev = ev_begin(c, 0);
-    if (flags & RT_FLAG_WAVEFRONT) { if (int r = render_wavefront(c, p, flags)) return r; }
-    else if (flags & RT_FLAG_ACCEL) {
-        rt::rt_render_kernel<rt::MODE_ACCEL><<<c->prop.multiProcessorCount * c->accel_bps, c->accel_tpb, accel_cta_smem_bytes(p.accel, c->accel_tpb), c->stream>>>(p);
-        ++c->launches;
-    } else if (flags & RT_FLAG_HALTON) {
-        rt::rt_render_kernel<rt::MODE_CULL, true><<<grid, c->tpb, smem, c->stream>>>(p);
-        ++c->launches;
-    } else {
-        if (flags & RT_FLAG_DEBUG_NO_CULL_) rt::rt_render_kernel<rt::MODE_NO_CULL><<<grid, c->tpb, smem, c->stream>>>(p);
-        else rt::rt_render_kernel<rt::MODE_CULL><<<grid, c->tpb, smem, c->stream>>>(p);
-        ++c->launches;
-    }
-    if (p.n_chunks > 1) {
-        rt::rt_combine_kernel<<<static_cast<unsigned>((n_pix + 255) / 256), 256, 0, c->stream>>>(p.hdr, p.partial, p.n_chunks, n_pix);
-        ++c->launches;
+    const int n_launch_lights = 1 + static_cast<int>(c->extra_lights.size());
+    for (int k = 0; k < n_launch_lights; ++k) {
+        if (k > 0) {                                     // light k alone, sky off, same paths; sample counts and path / closest-ray statistics come from pass 0
+            const rt_context::ExtraLight& e = c->extra_lights[k - 1];
+            p.Lx = e.L[0]; p.Ly = e.L[1]; p.Lz = e.L[2]; p.lcx = e.lc[0]; p.lcy = e.lc[1]; p.lcz = e.lc[2];
+            p.iLx = e.iL[0]; p.iLy = e.iL[1]; p.iLz = e.iL[2]; p.cullC = e.cullC;
+            p.skyx = p.skyy = p.skyz = 0.f; p.primary_pass = 0;
+        }
+        RT_CUDA(cudaMemsetAsync(c->counters, 0, sizeof(u64), c->stream));
+        if (flags & RT_FLAG_WAVEFRONT) { if (int r = render_wavefront(c, p, flags)) return r; }
+        else if (flags & RT_FLAG_ACCEL) {
+            rt::rt_render_kernel<rt::MODE_ACCEL><<<c->prop.multiProcessorCount * c->accel_bps, c->accel_tpb, accel_cta_smem_bytes(p.accel, c->accel_tpb), c->stream>>>(p);
+            ++c->launches;
+        } else if (flags & RT_FLAG_HALTON) {
+            rt::rt_render_kernel<rt::MODE_CULL, true><<<grid, c->tpb, smem, c->stream>>>(p);
+            ++c->launches;
+        } else {
+            if (flags & RT_FLAG_DEBUG_NO_CULL_) rt::rt_render_kernel<rt::MODE_NO_CULL><<<grid, c->tpb, smem, c->stream>>>(p);
+            else rt::rt_render_kernel<rt::MODE_CULL><<<grid, c->tpb, smem, c->stream>>>(p);
+            ++c->launches;
+        }
+        if (p.n_chunks > 1) {
+            rt::rt_combine_kernel<<<static_cast<unsigned>((n_pix + 255) / 256), 256, 0, c->stream>>>(p.hdr, p.partial, p.n_chunks, n_pix);
+            ++c->launches;
+        }
     }
     ev_end(c, ev);
     RT_CUDA(cudaGetLastError());

@@ -38,6 +38,7 @@ struct RenderParams {
                                  // [5] sphere tests evaluated for rays that asked for them (both query modes)
     AccelParams accel;           // RT_FLAG_ACCEL: box hierarchy image (rt_bvh.cuh)
     float iLx, iLy, iLz;         // safe_inv of the light direction (slab test of the shadow ray)
+    int primary_pass;            // 1: this launch owns the sample count and the path / closest-ray statistics; 0: an additional light's pass over the same paths
     u64* sampler;                // RT_FLAG_HALTON: [n_materials][2] = (m_reflectionProbabilitySampleIndex, m_sampleIndex), material.h:34,50-51,67
 };
 
@@ -284,8 +285,7 @@ __global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : RT_MAX
             }
             if (!want_closest && !want_shadow) {                                         // path complete
                 acc.x += Lsum.x * p.exposure; acc.y += Lsum.y * p.exposure; acc.z += Lsum.z * p.exposure;   // :182-183
-                acc.w += 1.0f;
-                ++n_paths;
+                if (p.primary_pass) { acc.w += 1.0f; ++n_paths; }
                 if (++s_cur < s_end) st = ST_NEW_PATH;
                 else {
                     if (p.n_chunks == 1) p.hdr[pix] = acc;
@@ -297,7 +297,7 @@ __global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : RT_MAX
     }
 
     // ---- stats: warp reduce, one atomic per warp ----
-    u64 c0 = n_closest, c1 = n_shadow, c3 = n_paths, c4 = n_skip;
+    u64 c0 = p.primary_pass ? n_closest : 0u, c1 = n_shadow, c3 = n_paths, c4 = n_skip;
     // sphere tests evaluated for rays that asked for them: every sphere per query (brute force), or the big spheres plus
     // 32 per visited group (box hierarchy)
     u64 c5 = (MODE == MODE_ACCEL)

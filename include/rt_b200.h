@@ -113,7 +113,9 @@ RT_API int  rt_scene_add_material_transparent(rt_scene* s, float smoothness, flo
 RT_API int  rt_scene_add_sphere(rt_scene* s, const float center[3], float radius, int material);
 /* Emissive(luminance, texture) as m_skyMaterial, spheres-app.cpp:120-121 */
 RT_API int  rt_scene_set_sky(rt_scene* s, float luminance, int texture);
-/* DirectionalLight(dir, XMCOLOR, luminance, occlusionTest) light.cpp:4-9; the occlusion callback is the scene itself. */
+/* DirectionalLight(dir, XMCOLOR, luminance, occlusionTest) light.cpp:4-9; the occlusion callback is the scene itself.
+ * May be called several times (m_lights, spheres-app.cpp:129): the first light is fused into the query pass, each further
+ * light adds one launch over the same paths per rt_render (counter RNG only). */
 RT_API int  rt_scene_add_directional_light(rt_scene* s, const float dir[3], const float rgba[4], float luminance);
 /* flat access (byte-identical input for an external checker) */
 RT_API int  rt_scene_counts(const rt_scene* s, int32_t* n_spheres, int32_t* n_materials, int32_t* n_textures, int32_t* n_lights);

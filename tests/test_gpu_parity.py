@@ -442,3 +442,33 @@ def test_halton_sampler_converges_to_reference_sampler(gpu, orc, scene_factory):
     assert got < 1.5 * floor + 1e-2
     with pytest.raises(rt.RtError):
         r.render(1, 50, rt.RT_FLAG_HALTON | rt.RT_FLAG_ACCEL)
+
+
+# ---------------------------------------------------------------- several lights (Material::Shade loops over m_lights, material.cpp:4-13)
+@pytest.mark.parametrize("flags_name", ["brute", "accel"])
+def test_several_lights_match_oracle(gpu, orc, flags_name):
+    """Lights 1.. are additional launches over the same paths (only that light on, sky off) into the same running sum;
+    the oracle evaluates the reference's per-vertex loop over all lights.  Same paths, same ray counters, radiance equal up
+    to the summation order (per light vs per vertex)."""
+    rt = gpu
+    flags = rt.RT_FLAG_ACCEL if flags_name == "accel" else 0
+    scene = rt.scenes.scene_d488()
+    scene.add_light(rt.DirectionalLight((-1.0, 0.6, 0.2), rt.XMCOLOR(0.3, 0.5, 1.0), 25000.0))
+    scene.add_light(rt.DirectionalLight((0.1, 1.0, -0.9), rt.XMCOLOR(1.0, 0.4, 0.3), 15000.0))
+    osc = orc.Scene.from_flat(scene.export())
+    w, h, spp = 160, 90, 20                       # 20 spp: chunked work items + combine in every pass
+    cam = rt.scenes.default_camera(aspect=w / h)
+    r = _renderer(rt, scene, cam, w, h)
+    r.reset_stats()
+    r.render(spp, 50, flags)
+    g, st = r.read_hdr_sum(), r.stats()
+    o, ost = orc.render(osc, orc_camera(orc, cam), orc.config(w, h, spp=spp))
+    assert np.all(g[..., 3] == spp)
+    assert (st.paths, st.closest_rays, st.shadow_rays) == (ost.paths, ost.closest_rays, ost.shadow_rays)
+    assert _close(g, o) < RTOL
+    # one light only differs (the extra lights do something)
+    r1 = _renderer(rt, rt.scenes.scene_d488(), cam, w, h)
+    r1.render(spp, 50, flags)
+    assert not np.allclose(r1.read_hdr_sum()[..., :3], g[..., :3], rtol=1e-3)
+    with pytest.raises(rt.RtError):
+        r.render(1, 50, rt.RT_FLAG_HALTON)
