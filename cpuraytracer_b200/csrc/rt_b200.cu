@@ -619,7 +619,7 @@ int rt_set_scene(rt_context* c, const rt_scene* s) {
     RT_CUDA(cudaFuncSetAttribute(rt::wf_intersect_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
     RT_CUDA(cudaFuncSetAttribute(rt::wf_intersect_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
     int best_tpb = 0, best_bps = 0;
-    for (int tpb = 256; tpb <= RT_MAX_TPB; tpb += 256) {
+    for (int tpb = 128; tpb <= RT_MAX_TPB; tpb += 128) {
         const size_t smem = cta_smem_bytes(n_pad, tpb);
         if (smem > static_cast<size_t>(optin)) break;
         int bps = 0;
