@@ -18,6 +18,33 @@ template<int SRC> __global__ void __launch_bounds__(256) k(float* out, const flo
   const float t = threadIdx.x*1e-3f;
   float ox2=0.1f+t, oy2=0.2f+t, oz2=0.3f+t, ndx=0.6f+t, ndy=0.5f, ndz=0.3f-t, noo=-t, od=1.f+t, oL=2.f+t;
   unsigned tot=0;
+  if (SRC == 2) {            // sphere data held in registers (4 pairs, reused): the FP2 + SHF mix of the loop without any load
+    float4 rA[4], rB[4]; float2 rC[4];
+    #pragma unroll
+    for (int q = 0; q < 4; ++q) { rA[q] = ((const float4*)sph)[q]; rB[q] = ((const float4*)sph)[npairs + q]; rC[q] = ((const float2*)sph)[4 * npairs + q]; }
+    for(int it=0; it<iters; ++it){
+      for(int g=0; g<npairs/16; ++g){
+        unsigned mc=0, ms=0;
+        #pragma unroll
+        for(int q=0;q<16;q++){
+          const float4 A = rA[q & 3], B = rB[q & 3]; const float2 C = rC[q & 3];
+          const u64 cx=pk(A.x,A.y), cy=pk(A.z,A.w), cz=pk(B.x,B.y), w=pk(B.z,B.w), cl=pk(C.x,C.y);
+          u64 c = fadd2(w, pk(noo,noo));
+          c = ffma2(pk(oz2,oz2), cz, c); c = ffma2(pk(oy2,oy2), cy, c); c = ffma2(pk(ox2,ox2), cx, c);
+          u64 b1 = ffma2(pk(ndz,ndz), cz, pk(od,od)); b1 = ffma2(pk(ndy,ndy), cy, b1); b1 = ffma2(pk(ndx,ndx), cx, b1);
+          u64 b2 = fadd2(cl, pk(oL,oL));
+          u64 d1 = ffma2(b1,b1,c), d2 = ffma2(b2,b2,c);
+          unsigned lo,hi;
+          upk(d1,lo,hi); mc = __funnelshift_l(lo, mc, 1); mc = __funnelshift_l(hi, mc, 1);
+          upk(d2,lo,hi); ms = __funnelshift_l(lo, ms, 1); ms = __funnelshift_l(hi, ms, 1);
+          noo += 1e-9f; od += 1e-9f;          // keep the iterations distinct (2 scalar FADD per pair)
+        }
+        tot += __popc(mc) + __popc(ms); noo += 1e-6f * (float)(tot & 1);
+      }
+    }
+    out[blockIdx.x*blockDim.x+threadIdx.x]=__uint_as_float(tot);
+    return;
+  }
   for(int it=0; it<iters; ++it){
     for(int g=0; g<npairs/16; ++g){
       unsigned mc=0, ms=0;
@@ -46,14 +73,14 @@ int main(){
   float* h=(float*)malloc(npairs*40); for(int i=0;i<npairs*10;i++) h[i]=(i%7)*0.37f-1.f; cudaMemcpy(sph,h,npairs*40,cudaMemcpyHostToDevice);
   cudaMemcpyToSymbol(cA, h, npairs*16); cudaMemcpyToSymbol(cB, h+npairs*4, npairs*16); cudaMemcpyToSymbol(cC, h+npairs*8, npairs*8);
   const int it=100;
-  for (int src = 0; src < 2; ++src) for (int bps : {2, 3, 4}) {
+  for (int src = 0; src < 3; ++src) for (int bps : {2, 3, 4}) {
     const int grid = sms*bps, threads = 256;
     cudaEvent_t e0,e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
-    auto f = [&]{ if (src) k<1><<<grid,threads,0>>>(out,sph,npairs,it); else k<0><<<grid,threads,npairs*40>>>(out,sph,npairs,it); };
+    auto f = [&]{ if (src == 2) k<2><<<grid,threads,0>>>(out,sph,npairs,it); else if (src) k<1><<<grid,threads,0>>>(out,sph,npairs,it); else k<0><<<grid,threads,npairs*40>>>(out,sph,npairs,it); };
     f(); cudaDeviceSynchronize(); cudaEventRecord(e0); f(); cudaEventRecord(e1); cudaEventSynchronize(e1);
     float ms; cudaEventElapsedTime(&ms,e0,e1);
     const double tests=(double)grid*threads*it*npairs*2*2;
-    printf("SRC %d (%s) thr %d bps %d: %.3f ms  %.3e tests/s  -> %.2f clk per pair per SMSP @1965\n", src, src ? "constant" : "shared", threads, bps, ms, tests/(ms*1e-3),
+    printf("SRC %d (%s) thr %d bps %d: %.3f ms  %.3e tests/s  -> %.2f clk per pair per SMSP @1965\n", src, src == 2 ? "registers" : src ? "constant" : "shared", threads, bps, ms, tests/(ms*1e-3),
            ms*1e-3*1.965e9 / ((double)it*npairs*(threads/32.0*bps/4.0)));
   }
   return 0;

@@ -27,10 +27,12 @@ template<int MODE> __global__ void __launch_bounds__(256) k(float* out, int iter
     for (int r = 0; r < 8; ++r) {
       #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        if (MODE == 0 || MODE == 1 || MODE == 4) a[j] = ffma2(a[j], mul, add);
+        if (MODE == 0 || MODE == 1 || MODE == 4 || MODE == 6 || MODE == 7) a[j] = ffma2(a[j], mul, add);
         if (MODE == 2 || MODE == 3) asm volatile("fma.rn.f32 %0, %0, %1, %2;" : "+f"(f[j]) : "f"(s), "f"(1e-7f));
         if (MODE == 5) { asm volatile("fma.rn.f32 %0, %0, %1, %2;" : "+f"(f[j]) : "f"(s), "f"(1e-7f)); asm volatile("fma.rn.f32 %0, %0, %1, %2;" : "+f"(f[j + 8]) : "f"(s), "f"(1e-7f)); }
         if (MODE == 1 || MODE == 3) asm volatile("shf.l.wrap.b32 %0, %0, %1, %2;" : "+r"(m[j]) : "r"(m[(j + 1) & 7]), "r"(sh));
+        if (MODE == 6 && (j & 1) == 1) { float2 v; asm volatile("ld.shared.v2.f32 {%0,%1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"((unsigned)__cvta_generic_to_shared(&sm[(r * 4 + (j >> 1)) & 63]))); acc4.x += v.x; }
+        if (MODE == 7 && (j & 3) == 3) { float4 v; asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"((unsigned)__cvta_generic_to_shared(&sm[(r * 2 + (j >> 2)) & 63]))); asm volatile("" :: "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)); }
         if (MODE == 4 && (j & 3) == 3) { float4 v; asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"((unsigned)__cvta_generic_to_shared(&sm[(r * 2 + (j >> 2)) & 63]))); acc4.x += v.x; }
       }
     }
@@ -62,5 +64,7 @@ int main(){
   run<3>("D  FFMA  x64 + SHF x64", out, sms, it, 64);
   run<4>("E  FFMA2 x64 + LDS.128 x16", out, sms, it, 128);
   run<5>("F  FFMA  x128 (clk per PAIR of FFMA)", out, sms, it, 128);
+  run<6>("G  FFMA2 x64 + LDS.64 x32 (+FADD each)", out, sms, it, 128);
+  run<7>("H  FFMA2 x64 + LDS.128 x16, result unused", out, sms, it, 128);
   return 0;
 }
