@@ -54,7 +54,7 @@ enum LaneState { ST_NEED_ITEM = 0, ST_NEW_PATH = 1, ST_IN_PATH = 2, ST_DONE = 3 
 // Shared-memory layout of one CTA: [cullA np*16][cullB np*16][cullC np*8][radius 2np*4][candidate lists 2*CAP*blockDim*4].
 // `lists` is this thread's column of the word-interleaved candidate lists (entry e at lists[e * blockDim.x]).
 #ifndef RT_MAX_TPB
-#define RT_MAX_TPB 768
+#define RT_MAX_TPB 896   /* launch bound of the brute-force kernels: 72 registers, no spills -> 7 CTAs x 128 threads = 28 warps per SM (r01t: +1 % over 768 / 80 registers) */
 #endif
 #ifdef RT_MIN_BLOCKS
 #define RT_RENDER_BOUNDS __launch_bounds__(RT_MAX_TPB, RT_MIN_BLOCKS)
