@@ -41,6 +41,9 @@ struct AccelParams {
 };
 
 #define RT_ACCEL_ENTRY_CAP 8          /* candidate-mask entries (2 words each) per lane; a full list is drained (E) before G goes on */
+#ifndef RT_ACCEL_FLAT_NODES
+#define RT_ACCEL_FLAT_NODES 4         /* up to this many L2 nodes the top level is skipped (every node counts as touched) */
+#endif
 #define RT_ACCEL_NODE_FLOATS 52       /* 8 children x (cx,cy,cz,hx,hy,hz) SoA = 48 floats, padded to 13 float4 (bank skew) */
 
 struct AccelSmem {
@@ -164,14 +167,20 @@ __device__ __forceinline__ QueryResult fused_query_accel(const AccelSmem& s, con
     const BoxRay rs = box_ray(o, invL.x, invL.y, invL.z, pad);
     const bool wc = want_closest, ws = want_shadow;
 
-    // ---- T: L2 boxes, converged ----
-    uint32_t m2 = 0u;
-    for (int j = 0; j < a.n2; ++j) {
-        const float4 b0 = s.top[2 * j], b1 = s.top[2 * j + 1];
-        const bool hit = (wc && box_touched(rc, b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, neg_t_slack)) ||
-                         (ws && box_touched(rs, b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, neg_t_slack));
-        if (hit) m2 |= 1u << j;
+    // ---- T: L2 boxes, converged.  Both rays are tested without a branch (a lane that does not want a ray masks the answer).
+    // With at most RT_ACCEL_FLAT_NODES L2 nodes (<= 1024 small spheres) their boxes are so large that nearly every ray touches
+    // them: the level is skipped and every lane runs M over all nodes, converged and with broadcast loads. ----
+    const bool flat = a.n2 <= RT_ACCEL_FLAT_NODES;
+    uint32_t m2 = flat ? ((1u << a.n2) - 1u) : 0u;
+    if (!flat) {
+        for (int j = 0; j < a.n2; ++j) {
+            const float4 b0 = s.top[2 * j], b1 = s.top[2 * j + 1];
+            const bool hc = box_touched(rc, b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, neg_t_slack);
+            const bool hs = box_touched(rs, b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, neg_t_slack);
+            if ((hc & wc) | (hs & ws)) m2 |= 1u << j;
+        }
     }
+    if (!(wc | ws)) m2 = 0u;
 
     // ---- M: group boxes of the touched L2 nodes ----
     uint32_t m2g = 0u;
@@ -186,9 +195,9 @@ __device__ __forceinline__ QueryResult fused_query_accel(const AccelSmem& s, con
             const float hxa[4] = {hx.x, hx.y, hx.z, hx.w}, hya[4] = {hy.x, hy.y, hy.z, hy.w}, hza[4] = {hz.x, hz.y, hz.z, hz.w};
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
-                const bool hit = (wc && box_touched(rc, cxa[k], cya[k], cza[k], hxa[k], hya[k], hza[k], neg_t_slack)) ||
-                                 (ws && box_touched(rs, cxa[k], cya[k], cza[k], hxa[k], hya[k], hza[k], neg_t_slack));
-                if (hit) byte |= 1u << (h * 4 + k);
+                const bool hc = box_touched(rc, cxa[k], cya[k], cza[k], hxa[k], hya[k], hza[k], neg_t_slack);
+                const bool hs = box_touched(rs, cxa[k], cya[k], cza[k], hxa[k], hya[k], hza[k], neg_t_slack);
+                if ((hc & wc) | (hs & ws)) byte |= 1u << (h * 4 + k);
             }
         }
         if (byte) {
