@@ -420,7 +420,7 @@ static int build_accel(rt_context* c, const rt_scene* s) {
     a.blob = c->accel_blob; a.blob_bytes = static_cast<int>(total);
     a.off_B = static_cast<int>(off_B); a.off_R = static_cast<int>(off_R); a.off_I = static_cast<int>(off_I);
     a.off_box = static_cast<int>(off_box); a.off_top = static_cast<int>(off_top);
-    a.n_pairs = np; a.n_big_groups = n_big_groups; a.n_groups = n_groups; a.n2 = n2; a.gmask_words = std::max(1, (n2 + 3) / 4);
+    a.n_pairs = np; a.n_big_groups = n_big_groups; a.n_big_pairs = (static_cast<int>(big.size()) + 1) / 2; a.n_groups = n_groups; a.n2 = n2; a.gmask_words = std::max(1, (n2 + 3) / 4);
     // CTA size: most resident warps per SM next to one image copy per CTA
     const int optin = static_cast<int>(c->prop.sharedMemPerBlockOptin);
     RT_CUDA(cudaFuncSetAttribute(rt::rt_render_kernel<rt::MODE_ACCEL>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));

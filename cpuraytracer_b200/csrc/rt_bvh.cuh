@@ -16,7 +16,7 @@
 // Schedule of one query (per lane; lanes of a warp run the same phase together):
 //   T  top             converged loop over the n2 L2 boxes                       -> bit mask m2 of touched L2 nodes
 //   M  middle          per lane: pop an L2 node, test its 8 group boxes          -> one byte per L2 node in shared memory
-//   G  groups          the big groups first (every lane, same addresses: broadcast LDS), then per lane: pop a touched group,
+//   G  groups          the big spheres first (every lane, same addresses: broadcast LDS), then per lane: pop a touched group,
 //                      cull its 16 sphere pairs for both rays (pair order XOR-swizzled by the lane id so that the
 //                      quarter-warps' LDS.128 hit 8 different bank groups)       -> candidate-mask entries
 //   E  exact           per lane: walk the entries, exact test per candidate
@@ -32,6 +32,7 @@ struct AccelParams {
     int off_B, off_R, off_I, off_box, off_top;   // byte offsets of the sections (A starts at 0)
     int n_pairs;             // sphere pairs in the image (big groups + small groups, each padded to 32 slots)
     int n_big_groups;        // groups that are always culled
+    int n_big_pairs;         // sphere pairs of the big groups that hold spheres (the rest of the last big group is padding)
     int n_groups;            // small groups (Morton order)
     int n2;                  // L2 nodes = ceil(n_groups / 8), <= 32
     int gmask_words;         // per-thread scratch words holding one byte per L2 node
@@ -209,25 +210,31 @@ __device__ __forceinline__ QueryResult fused_query_accel(const AccelSmem& s, con
     // ---- G + E.  One copy of each in the code: G runs until this lane's groups are exhausted or its entry list is
     // full, E drains the list; the outer loop repeats only after an overflow (rare). ----
     const int rot_lane = static_cast<int>(lane & 15u);
-    int big = 0;                                            // big groups still to cull (all lanes, first)
+    int ne = 0;
+    // big groups (every lane, converged, broadcast loads): only the pairs that hold spheres -- 2 of 16 in the default scene
+    for (int bg = 0; bg < a.n_big_groups; ++bg) {
+        const int np_g = min(16, a.n_big_pairs - 16 * bg);
+        uint32_t mc = 0u, ms = 0u;
+#pragma unroll 2
+        for (int q = 0; q < np_g; ++q) cull_pair2(cr, s.sA[bg * 16 + q], s.sB[bg * 16 + q], mc, ms);
+        const uint32_t valid = 0xffffffffu << (32 - 2 * np_g);           // bit 31 = first sphere of the group, as everywhere
+        const uint32_t cc = ~(mc << (32 - 2 * np_g)) & valid & en_c, cs = ~(ms << (32 - 2 * np_g)) & valid & en_s;
+        if (cc) { ent[(2 * ne) * lstride] = cc; ent[(2 * ne + 1) * lstride] = static_cast<uint32_t>(bg * 32); ++ne; }
+        if (cs) { ent[(2 * ne) * lstride] = cs; ent[(2 * ne + 1) * lstride] = static_cast<uint32_t>(bg * 32) | 0x80000000u; ++ne; }
+    }
     uint32_t cur8 = 0u; int curj = 0;
     bool more = true;
     while (more) {
-        int ne = 0;
         for (;;) {
             if (ne > RT_ACCEL_ENTRY_CAP - 2) break;         // a group adds at most two entries
-            int slot_base, rot;
-            if (big < a.n_big_groups) { slot_base = big * 32; rot = 0; ++big; }
-            else {
-                if (cur8 == 0u) {
-                    if (m2g == 0u) { more = false; break; }
-                    curj = __ffs(m2g) - 1; m2g &= m2g - 1u;
-                    cur8 = reinterpret_cast<const unsigned char*>(gm + (curj >> 2) * lstride)[curj & 3];
-                }
-                const int k = __ffs(cur8) - 1; cur8 &= cur8 - 1u;
-                slot_base = (a.n_big_groups + curj * 8 + k) * 32; rot = rot_lane;
-                cnt.group_visits += (en_c & 1u) + (en_s & 1u);
+            if (cur8 == 0u) {
+                if (m2g == 0u) { more = false; break; }
+                curj = __ffs(m2g) - 1; m2g &= m2g - 1u;
+                cur8 = reinterpret_cast<const unsigned char*>(gm + (curj >> 2) * lstride)[curj & 3];
             }
+            const int k = __ffs(cur8) - 1; cur8 &= cur8 - 1u;
+            const int slot_base = (a.n_big_groups + curj * 8 + k) * 32, rot = rot_lane;
+            cnt.group_visits += (en_c & 1u) + (en_s & 1u);
             // pair q of this step is pair (q ^ rot) of the group: an XOR on a 256-byte aligned group is one LOP3 per address, and
             // inside a quarter-warp (8 consecutive lanes) the 8 addresses fall into 8 different 16-byte bank groups.  The
             // candidate masks stay in visiting order; E undoes the permutation per candidate (slot = base + (bit ^ 2 rot)).
@@ -257,6 +264,7 @@ __device__ __forceinline__ QueryResult fused_query_accel(const AccelSmem& s, con
                 else { const int idx = s.sI[slot]; if (closer(t, idx, res)) { res.t = t; res.idx = idx; res.slot = slot; } }
             }
         }
+        ne = 0;
     }
     return res;
 }

@@ -301,7 +301,7 @@ __global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : RT_MAX
     // sphere tests evaluated for rays that asked for them: every sphere per query (brute force), or the big spheres plus
     // 32 per visited group (box hierarchy)
     u64 c5 = (MODE == MODE_ACCEL)
-        ? static_cast<u64>(p.accel.n_big_groups * 32) * (n_closest + n_shadow - n_skip) + 32ull * acnt.group_visits
+        ? static_cast<u64>(p.accel.n_big_pairs * 2) * (n_closest + n_shadow - n_skip) + 32ull * acnt.group_visits
         : static_cast<u64>(p.n_spheres) * (n_closest + n_shadow - n_skip);
     for (int off = 16; off > 0; off >>= 1) {
         c0 += __shfl_down_sync(FULL, c0, off); c1 += __shfl_down_sync(FULL, c1, off); c3 += __shfl_down_sync(FULL, c3, off);
