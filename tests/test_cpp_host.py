@@ -234,3 +234,16 @@ def test_cpp_ranlux_scene_equals_python_replay(host, rt, tmp_path, seed):
     assert sp.tobytes() == flat.spheres.tobytes()
     assert ma.tobytes() == flat.materials.tobytes()
     assert te.tobytes() == flat.textures.tobytes()
+
+
+@pytest.mark.gpu
+def test_cli_accel_flag_renders_the_same_bits(host, tmp_path):
+    """apps/spheres --accel (RT_FLAG_ACCEL through rt_group_render) == the default brute-force query, byte for byte."""
+    w, h = 200, 120
+    base = ["--width", w, "--height", h, "--scene", "d488", "--quiet", "--format", "exr", "--spp", 5]
+    run_cli(host[1], *base, "--out", tmp_path / "brute")
+    r = run_cli(host[1], *base, "--out", tmp_path / "accel", "--accel")
+    a, na = read_exr(tmp_path / "brute.exr")
+    b, nb = read_exr(tmp_path / "accel.exr")
+    assert na == nb == 5 and np.array_equal(a, b)
+    assert json.loads(r.stdout.strip().splitlines()[-1])["paths"] == w * h * 5
