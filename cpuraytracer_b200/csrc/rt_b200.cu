@@ -14,6 +14,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -299,6 +300,12 @@ static uint32_t morton_spread10(uint32_t v) {
 }
 static float round_up(double x) { float f = static_cast<float>(x); if (static_cast<double>(f) < x) f = std::nextafter(f, INFINITY); return f; }
 
+// The accel kernels are instantiated for 8, 16 and 32 slots per small group (template argument GSHIFT).
+template <int G> static const void* accel_render_fn() { return reinterpret_cast<const void*>(&rt::rt_render_kernel<rt::MODE_ACCEL, false, G>); }
+template <int G> static const void* accel_primary_fn() { return reinterpret_cast<const void*>(&rt::rt_primary_kernel<rt::MODE_ACCEL, G>); }
+static const void* accel_render_kernel(int gshift) { return gshift == 3 ? accel_render_fn<3>() : gshift == 4 ? accel_render_fn<4>() : accel_render_fn<5>(); }
+static const void* accel_primary_kernel(int gshift) { return gshift == 3 ? accel_primary_fn<3>() : gshift == 4 ? accel_primary_fn<4>() : accel_primary_fn<5>(); }
+
 static int build_accel(rt_context* c, const rt_scene* s) {
     c->accel_ok = false; c->accel_why.clear();
     rt::AccelParams& a = c->base.accel;
@@ -329,17 +336,26 @@ static int build_accel(rt_context* c, const rt_scene* s) {
     }
     std::stable_sort(keyed.begin(), keyed.end(), [](const std::pair<uint32_t, int>& x, const std::pair<uint32_t, int>& y) { return x.first < y.first; });
     const int n_big_groups = (static_cast<int>(big.size()) + 31) / 32;
-    const int n_groups = (static_cast<int>(small.size()) + 31) / 32;
+    // Slots per small group: the finest of 8 / 16 / 32 whose group count still fits the 32 x 8 fan-out of the two box levels
+    // (a ray then culls fewer spheres per touched box; measured in profiles/r01x_accel_group_size.txt).  RT_ACCEL_GSHIFT
+    // (3, 4 or 5) sets the finest size tried, for experiments.
+    int gshift = 3;
+    if (const char* e = std::getenv("RT_ACCEL_GSHIFT")) { const int v = std::atoi(e); if (v >= 3 && v <= 5) gshift = v; }
+    while (gshift < 5 && (static_cast<int>(small.size()) + (1 << gshift) - 1) / (1 << gshift) > RT_ACCEL_GSHIFT_MAX_GROUPS) ++gshift;
+    const int GS = 1 << gshift;
+    const int n_groups = (static_cast<int>(small.size()) + GS - 1) / GS;
     const int n2 = (n_groups + 7) / 8;
-    if (n2 > 32) { c->accel_why = "more than 8192 small spheres (the L2 mask is one 32-bit word)"; return RT_OK; }
-    const int n_slots = (n_big_groups + n_groups) * 32;
+    if (n2 > 32) { c->accel_why = "too many small spheres for this group size (the L2 mask is one 32-bit word: at most 8192 with 32-slot groups)"; return RT_OK; }
+    const int small_base = n_big_groups * 32;
+    const int n_slots = small_base + n_groups * GS;
     std::vector<int> slot_orig(std::max(n_slots, 1), -1);
     for (size_t k = 0; k < big.size(); ++k) slot_orig[k] = big[k];
-    for (size_t k = 0; k < keyed.size(); ++k) slot_orig[n_big_groups * 32 + k] = keyed[k].second;
+    for (size_t k = 0; k < keyed.size(); ++k) slot_orig[small_base + k] = keyed[k].second;
     const int np = n_slots / 2;
-    // sections
+    // sections (A and B start on 256-byte boundaries: the XOR-swizzled group loads rely on aligned groups)
     auto align16 = [](size_t x) { return (x + 15u) & ~static_cast<size_t>(15u); };
-    const size_t off_A = 0, off_B = off_A + static_cast<size_t>(np) * 16, off_R = off_B + static_cast<size_t>(np) * 16;
+    auto align256 = [](size_t x) { return (x + 255u) & ~static_cast<size_t>(255u); };
+    const size_t off_A = 0, off_B = align256(off_A + static_cast<size_t>(np) * 16), off_R = off_B + static_cast<size_t>(np) * 16;
     const size_t off_I = align16(off_R + static_cast<size_t>(n_slots) * 4);
     const size_t off_box = align16(off_I + static_cast<size_t>(n_slots) * 2);
     const size_t off_top = off_box + static_cast<size_t>(n2) * RT_ACCEL_NODE_FLOATS * 4;
@@ -377,8 +393,8 @@ static int build_accel(rt_context* c, const rt_scene* s) {
     Box all = empty_box();
     double r_min = 1e300, r_max = 0;
     for (int g = 0; g < n_groups; ++g)
-        for (int j = 0; j < 32; ++j) {
-            const int i = slot_orig[(n_big_groups + g) * 32 + j];
+        for (int j = 0; j < GS; ++j) {
+            const int i = slot_orig[small_base + g * GS + j];
             if (i < 0) continue;
             const rt_sphere_desc& sp = s->spheres[i];
             Box b; b.any = true; const double cc[3] = {sp.cx, sp.cy, sp.cz};
@@ -420,17 +436,17 @@ static int build_accel(rt_context* c, const rt_scene* s) {
     a.blob = c->accel_blob; a.blob_bytes = static_cast<int>(total);
     a.off_B = static_cast<int>(off_B); a.off_R = static_cast<int>(off_R); a.off_I = static_cast<int>(off_I);
     a.off_box = static_cast<int>(off_box); a.off_top = static_cast<int>(off_top);
-    a.n_pairs = np; a.n_big_groups = n_big_groups; a.n_big_pairs = (static_cast<int>(big.size()) + 1) / 2; a.n_groups = n_groups; a.n2 = n2; a.gmask_words = std::max(1, (n2 + 3) / 4);
+    a.n_pairs = np; a.n_big_groups = n_big_groups; a.n_big_pairs = (static_cast<int>(big.size()) + 1) / 2; a.n_groups = n_groups; a.gshift = gshift; a.n2 = n2; a.gmask_words = std::max(1, (n2 + 3) / 4);
     // CTA size: most resident warps per SM next to one image copy per CTA
     const int optin = static_cast<int>(c->prop.sharedMemPerBlockOptin);
-    RT_CUDA(cudaFuncSetAttribute(rt::rt_render_kernel<rt::MODE_ACCEL>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
-    RT_CUDA(cudaFuncSetAttribute(rt::rt_primary_kernel<rt::MODE_ACCEL>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
+    RT_CUDA(cudaFuncSetAttribute(accel_render_kernel(gshift), cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
+    RT_CUDA(cudaFuncSetAttribute(accel_primary_kernel(gshift), cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
     int best_tpb = 0, best_bps = 0;
     for (int tpb = 128; tpb <= RT_ACCEL_MAX_TPB; tpb += 128) {
         const size_t smem = accel_cta_smem_bytes(a, tpb);
         if (smem > static_cast<size_t>(optin)) break;
         int bps = 0;
-        RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, rt::rt_render_kernel<rt::MODE_ACCEL>, tpb, smem));
+        RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, accel_render_kernel(gshift), tpb, smem));
         if (bps * tpb > best_bps * best_tpb) { best_tpb = tpb; best_bps = bps; }
     }
     if (best_bps < 1) { c->accel_why = "the hierarchy image does not fit in shared memory"; return RT_OK; }
@@ -793,7 +809,9 @@ int rt_render(rt_context* c, uint64_t first_sample, int spp, int max_depth, uint
         RT_CUDA(cudaMemsetAsync(c->counters, 0, sizeof(u64), c->stream));
         if (flags & RT_FLAG_WAVEFRONT) { if (int r = render_wavefront(c, p, flags)) return r; }
         else if (flags & RT_FLAG_ACCEL) {
-            rt::rt_render_kernel<rt::MODE_ACCEL><<<c->prop.multiProcessorCount * c->accel_bps, c->accel_tpb, accel_cta_smem_bytes(p.accel, c->accel_tpb), c->stream>>>(p);
+            void* args[] = {const_cast<rt::RenderParams*>(&p)};
+            RT_CUDA(cudaLaunchKernel(accel_render_kernel(p.accel.gshift), dim3(c->prop.multiProcessorCount * c->accel_bps), dim3(c->accel_tpb), args,
+                                     accel_cta_smem_bytes(p.accel, c->accel_tpb), c->stream));
             ++c->launches;
         } else if (flags & RT_FLAG_HALTON) {
             rt::rt_render_kernel<rt::MODE_CULL, true><<<grid, c->tpb, smem, c->stream>>>(p);
@@ -862,7 +880,12 @@ int rt_primary_hits(rt_context* c, uint64_t sample, uint32_t flags, int32_t* sph
     const size_t smem = cta_smem_bytes(c->n_pad, c->tpb);
     const int grid = c->prop.multiProcessorCount * std::max(1, c->render_blocks_per_sm);
     if ((flags & RT_FLAG_ACCEL) && !c->accel_ok) return fail(RT_ERR_UNSUPPORTED, "rt_primary_hits: RT_FLAG_ACCEL unavailable for this scene: %s", c->accel_why.c_str());
-    if (flags & RT_FLAG_ACCEL) rt::rt_primary_kernel<rt::MODE_ACCEL><<<c->prop.multiProcessorCount * c->accel_bps, c->accel_tpb, accel_cta_smem_bytes(p.accel, c->accel_tpb), c->stream>>>(p, c->ids, c->mids);
+    if (flags & RT_FLAG_ACCEL) {
+        int32_t* a_ids = c->ids; int32_t* a_mids = c->mids;
+        void* args[] = {&p, &a_ids, &a_mids};
+        RT_CUDA(cudaLaunchKernel(accel_primary_kernel(p.accel.gshift), dim3(c->prop.multiProcessorCount * c->accel_bps), dim3(c->accel_tpb), args,
+                                 accel_cta_smem_bytes(p.accel, c->accel_tpb), c->stream));
+    }
     else if (flags & RT_FLAG_DEBUG_NO_CULL_) rt::rt_primary_kernel<rt::MODE_NO_CULL><<<grid, c->tpb, smem, c->stream>>>(p, c->ids, c->mids);
     else rt::rt_primary_kernel<rt::MODE_CULL><<<grid, c->tpb, smem, c->stream>>>(p, c->ids, c->mids);
     ++c->launches;

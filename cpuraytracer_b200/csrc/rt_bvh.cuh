@@ -33,7 +33,8 @@ struct AccelParams {
     int n_pairs;             // sphere pairs in the image (big groups + small groups, each padded to 32 slots)
     int n_big_groups;        // groups that are always culled
     int n_big_pairs;         // sphere pairs of the big groups that hold spheres (the rest of the last big group is padding)
-    int n_groups;            // small groups (Morton order)
+    int n_groups;            // small groups (Morton order), 2^gshift slots each
+    int gshift;              // log2 of the slots per small group: 3, 4 or 5 (chosen per scene by build_accel; kernel template argument)
     int n2;                  // L2 nodes = ceil(n_groups / 8), <= 32
     int gmask_words;         // per-thread scratch words holding one byte per L2 node
     float csx, csy, csz, cs_radius;   // bounding sphere of the small spheres (centres + radii)
@@ -45,6 +46,7 @@ struct AccelParams {
 #ifndef RT_ACCEL_FLAT_NODES
 #define RT_ACCEL_FLAT_NODES 4         /* up to this many L2 nodes the top level is skipped (every node counts as touched) */
 #endif
+#define RT_ACCEL_GSHIFT_MAX_GROUPS 256 /* 32 L2 nodes x 8 groups */
 #define RT_ACCEL_NODE_FLOATS 52       /* 8 children x (cx,cy,cz,hx,hy,hz) SoA = 48 floats, padded to 13 float4 (bank skew) */
 
 struct AccelSmem {
@@ -134,6 +136,7 @@ struct AccelCounters { uint32_t group_visits; };
 
 // Same contract as fused_query(): closest hit along (o,d) and occlusion along (o,L).  res.idx is the ORIGINAL sphere
 // index, res.slot the position in the re-ordered image (for the hit record's centre / radius).
+template <int GSHIFT>
 __device__ __forceinline__ QueryResult fused_query_accel(const AccelSmem& s, const AccelParams& a, int lstride,
                                                          V3 o, V3 d, V3 L, V3 invL, bool want_closest, bool want_shadow, AccelCounters& cnt) {
     QueryResult res; res.t = 0.f; res.idx = -1; res.slot = -1; res.occluded = false;
@@ -209,7 +212,8 @@ __device__ __forceinline__ QueryResult fused_query_accel(const AccelSmem& s, con
 
     // ---- G + E.  One copy of each in the code: G runs until this lane's groups are exhausted or its entry list is
     // full, E drains the list; the outer loop repeats only after an overflow (rare). ----
-    const int rot_lane = static_cast<int>(lane & 15u);
+    constexpr int kGS = 1 << GSHIFT, kPPG = kGS / 2;                  // slots / sphere pairs of one small group
+    const int rot_lane = static_cast<int>(lane & static_cast<unsigned>(kPPG - 1));
     int ne = 0;
     // big groups (every lane, converged, broadcast loads): only the pairs that hold spheres -- 2 of 16 in the default scene
     for (int bg = 0; bg < a.n_big_groups; ++bg) {
@@ -233,17 +237,19 @@ __device__ __forceinline__ QueryResult fused_query_accel(const AccelSmem& s, con
                 cur8 = reinterpret_cast<const unsigned char*>(gm + (curj >> 2) * lstride)[curj & 3];
             }
             const int k = __ffs(cur8) - 1; cur8 &= cur8 - 1u;
-            const int slot_base = (a.n_big_groups + curj * 8 + k) * 32, rot = rot_lane;
+            const int slot_base = a.n_big_groups * 32 + (curj * 8 + k) * kGS, rot = rot_lane;
             cnt.group_visits += (en_c & 1u) + (en_s & 1u);
-            // pair q of this step is pair (q ^ rot) of the group: an XOR on a 256-byte aligned group is one LOP3 per address, and
+            // pair q of this step is pair (q ^ rot) of the group: an XOR on a (16 kPPG)-byte aligned group is one LOP3 per address, and
             // inside a quarter-warp (8 consecutive lanes) the 8 addresses fall into 8 different 16-byte bank groups.  The
             // candidate masks stay in visiting order; E undoes the permutation per candidate (slot = base + (bit ^ 2 rot)).
             const uint32_t pa = sa32 + static_cast<uint32_t>(slot_base) * 8u + (static_cast<uint32_t>(rot) << 4);
             const uint32_t pb = sb32 + static_cast<uint32_t>(slot_base) * 8u + (static_cast<uint32_t>(rot) << 4);
             uint32_t mc = 0u, ms = 0u;
 #pragma unroll
-            for (int q = 0; q < 16; ++q) cull_pair2(cr, lds128(pa ^ (q << 4)), lds128(pb ^ (q << 4)), mc, ms);
-            const uint32_t cc = ~mc & en_c, cs = ~ms & en_s;
+            for (int q = 0; q < kPPG; ++q) cull_pair2(cr, lds128(pa ^ (q << 4)), lds128(pb ^ (q << 4)), mc, ms);
+            // bit 31 = first slot of the group, as everywhere; a group smaller than 32 slots leaves the low bits clear
+            const uint32_t gvalid = 0xffffffffu << (32 - kGS);
+            const uint32_t cc = ~(mc << (32 - kGS)) & gvalid & en_c, cs = ~(ms << (32 - kGS)) & gvalid & en_s;
             const uint32_t meta = static_cast<uint32_t>(slot_base) | (static_cast<uint32_t>(rot) << 25);
             if (cc) { ent[(2 * ne) * lstride] = cc; ent[(2 * ne + 1) * lstride] = meta; ++ne; }
             if (cs) { ent[(2 * ne) * lstride] = cs; ent[(2 * ne + 1) * lstride] = meta | 0x80000000u; ++ne; }

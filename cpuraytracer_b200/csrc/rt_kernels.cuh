@@ -175,7 +175,7 @@ enum { MODE_CULL = 0, MODE_NO_CULL = 1, MODE_ACCEL = 2 };
 #define RT_ACCEL_MAX_TPB 640
 #endif
 /* the hierarchy walk keeps two sets of slab constants live: 128 registers per thread */
-template <int MODE, bool HALTON = false>
+template <int MODE, bool HALTON = false, int GSHIFT = 5>
 __global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : RT_MAX_TPB) rt_render_kernel(const RenderParams p) {
     extern __shared__ __align__(256) unsigned char smem[];
     float4 *sA = nullptr, *sB = nullptr; float2* sC = nullptr; float* sR = nullptr; uint32_t* lists = nullptr;
@@ -241,7 +241,7 @@ __global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : RT_MAX
 
         // ---- K2+K3: fused closest-hit / shadow query over every sphere ----
         QueryResult q;
-        if constexpr (MODE == MODE_ACCEL) q = fused_query_accel(av, p.accel, lstride, o, d, Ldir, invL, active && want_closest, active && want_shadow, acnt);
+        if constexpr (MODE == MODE_ACCEL) q = fused_query_accel<GSHIFT>(av, p.accel, lstride, o, d, Ldir, invL, active && want_closest, active && want_shadow, acnt);
         else q = fused_query<MODE == MODE_NO_CULL>(sA, sB, sC, sR, lists, lstride, p.n_groups, p.n_spheres, o, d, Ldir, active && want_closest, active && want_shadow);
         ++n_pass;
 
@@ -299,9 +299,9 @@ __global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : RT_MAX
     // ---- stats: warp reduce, one atomic per warp ----
     u64 c0 = p.primary_pass ? n_closest : 0u, c1 = n_shadow, c3 = n_paths, c4 = n_skip;
     // sphere tests evaluated for rays that asked for them: every sphere per query (brute force), or the big spheres plus
-    // 32 per visited group (box hierarchy)
+    // 2^GSHIFT per visited group (box hierarchy)
     u64 c5 = (MODE == MODE_ACCEL)
-        ? static_cast<u64>(p.accel.n_big_pairs * 2) * (n_closest + n_shadow - n_skip) + 32ull * acnt.group_visits
+        ? static_cast<u64>(p.accel.n_big_pairs * 2) * (n_closest + n_shadow - n_skip) + static_cast<u64>(1 << GSHIFT) * acnt.group_visits
         : static_cast<u64>(p.n_spheres) * (n_closest + n_shadow - n_skip);
     for (int off = 16; off > 0; off >>= 1) {
         c0 += __shfl_down_sync(FULL, c0, off); c1 += __shfl_down_sync(FULL, c1, off); c3 += __shfl_down_sync(FULL, c3, off);
@@ -368,7 +368,7 @@ __global__ void __launch_bounds__(256) rt_resolve_kernel(const float4* __restric
 }
 
 // K6: primary-hit id buffers (jitter/lens per flags) for frame `first_sample`.
-template <int MODE>
+template <int MODE, int GSHIFT = 5>
 __global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : RT_MAX_TPB) rt_primary_kernel(const RenderParams p, int32_t* __restrict__ sphere_idx, int32_t* __restrict__ material_id) {
     extern __shared__ __align__(256) unsigned char smem[];
     float4 *sA = nullptr, *sB = nullptr; float2* sC = nullptr; float* sR = nullptr; uint32_t* lists = nullptr;
@@ -390,7 +390,7 @@ __global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : RT_MAX
             camera_get_ray(p.cam, u, v, lx, ly, o, d);
         }
         QueryResult q;
-        if constexpr (MODE == MODE_ACCEL) q = fused_query_accel(av, p.accel, static_cast<int>(blockDim.x), o, d, mk3(p.Lx, p.Ly, p.Lz), mk3(p.iLx, p.iLy, p.iLz), valid, false, acnt);
+        if constexpr (MODE == MODE_ACCEL) q = fused_query_accel<GSHIFT>(av, p.accel, static_cast<int>(blockDim.x), o, d, mk3(p.Lx, p.Ly, p.Lz), mk3(p.iLx, p.iLy, p.iLz), valid, false, acnt);
         else q = fused_query<MODE == MODE_NO_CULL>(sA, sB, sC, sR, lists, static_cast<int>(blockDim.x), p.n_groups, p.n_spheres, o, d, mk3(p.Lx, p.Ly, p.Lz), valid, false);
         if (valid) {
             const int pix = py * p.W + px;
