@@ -363,7 +363,7 @@ def run_b200(args):
             "gpu_launches": int(counts[4].item()),
             "e2e": {"value": e2e_value, "unit": "path samples/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
             "roofline": {"bound": "fp32", "achieved": achieved, "peak": FP32_PEAK_MEASURED_TFLOPS, "unit": "TFLOP/s",
-                         "frac": achieved / FP32_PEAK_MEASURED_TFLOPS, "traffic": None,
+                         "frac": achieved / FP32_PEAK_MEASURED_TFLOPS, "traffic": _ncu_traffic(args.workload, args.query),
                          "note": "rt_render_kernel: sphere tests x 17 flop / kernel time (cudaEvents on its stream); peak = measured "
                                  "FFMA-chain FP32 rate (MEASURED_PEAKS.json has no FP32 figure; nominal 148x128x2x1.965 GHz = 74.5)",
                          "sphere_tests_per_s": tests / kern_s / world, "kernel_ms_per_step": 1e3 * kern_s / args.steps},
@@ -381,6 +381,17 @@ def run_b200(args):
         dist.barrier()
         dist.destroy_process_group()
     return 0
+
+
+def _ncu_traffic(workload: str, query: str):
+    """dram__bytes_read.sum + dram__bytes_write.sum of ONE rt_render_kernel launch of this workload's step (same scene, size,
+    spp per step and depth), from the committed ncu capture (profiles/traffic.json, written from tools/gpu_round.sh's
+    `traffic_*.csv`); None when no capture of that launch exists.  A profiler number, never measured inside bench.py."""
+    try:
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "traffic.json")) as f:
+            return json.load(f).get(f"{workload}:{query}", {}).get("bytes")
+    except (OSError, ValueError):
+        return None
 
 
 def _emit(line: dict) -> None:

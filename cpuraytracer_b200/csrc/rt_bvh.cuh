@@ -42,7 +42,9 @@ struct AccelParams {
     float c_max;                      // largest |coordinate| of any small-sphere box face
 };
 
+#ifndef RT_ACCEL_ENTRY_CAP
 #define RT_ACCEL_ENTRY_CAP 8          /* candidate-mask entries (2 words each) per lane; a full list is drained (E) before G goes on */
+#endif
 #ifndef RT_ACCEL_FLAT_NODES
 #define RT_ACCEL_FLAT_NODES 4         /* up to this many L2 nodes the top level is skipped (every node counts as touched) */
 #endif
@@ -91,8 +93,17 @@ __device__ __forceinline__ void cull_pair2(const CullRay2& r, const float4 A, co
     const u64 d1 = ffma2(b1, b1, nc2);
     const u64 d2 = ffma2(b2, b2, nc2);
     uint32_t lo, hi;
+#if RT_CULL_DIRFILTER
+    uint32_t blo, bhi, nlo, nhi;                             // as cull_pair(): centre behind the origin and origin outside = miss
+    upk2(nc2, nlo, nhi);
+    upk2(d1, lo, hi); upk2(b1, blo, bhi); lo |= ~blo & nlo; hi |= ~bhi & nhi;
+    mc = __funnelshift_l(lo, mc, 1); mc = __funnelshift_l(hi, mc, 1);
+    upk2(d2, lo, hi); upk2(b2, blo, bhi); lo |= ~blo & nlo; hi |= ~bhi & nhi;
+    ms = __funnelshift_l(lo, ms, 1); ms = __funnelshift_l(hi, ms, 1);
+#else
     upk2(d1, lo, hi); mc = __funnelshift_l(lo, mc, 1); mc = __funnelshift_l(hi, mc, 1);
     upk2(d2, lo, hi); ms = __funnelshift_l(lo, ms, 1); ms = __funnelshift_l(hi, ms, 1);
+#endif
 }
 
 // Slab test constants of one ray.  A box (centre c, half extent h) is touched when, per axis k,

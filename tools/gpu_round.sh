@@ -22,6 +22,13 @@ python bench.py --steps 2 --warmup 3 --no-cpu-baseline > "$OUT/bench_short.json"
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file "$OUT/launches.csv" \
     python bench.py --steps 2 --warmup 3 --no-cpu-baseline > "$OUT/ncu_launches.log" 2>&1
 echo "ncu launches exit $?"
+# ncu: HBM traffic of one render-kernel launch of the default bench step (c3: 256 spp, depth 50) in both query modes -> roofline.traffic
+for q in "brute 0" "accel 8"; do
+  set -- $q
+  ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum --clock-control none -k regex:rt_render_kernel -s 1 -c 1 --csv \
+      --log-file "$OUT/traffic_c3_$1.csv" python tools/ncu_case.py d488 1920 1080 256 50 $2 > "$OUT/ncu_traffic_$1.log" 2>&1
+  echo "ncu traffic $1 exit $?"
+done
 # ncu: full set on the render kernel, short case (second launch = warm): brute force, then RT_FLAG_ACCEL on both scenes
 python tools/ncu_case.py d488 1920 1080 16 50 > "$OUT/ncu_case_plain.log" 2>&1 &&
 ncu --set full --clock-control none --import-source on -k regex:rt_render_kernel -s 1 -c 1 -o "$OUT/prof_render" \
