@@ -348,6 +348,7 @@ def _random_scene(rt, rng, n, radius_spread, extent, with_ground):
     (4, 1000, 50.0, 10.0, True),    # radii over 1.7 decades: some spheres become "big", heavy overlap
     (5, 2500, 8.0, 40.0, False),    # free-floating cloud, 10 L2 nodes
     (6, 700, 20.0, 300.0, True),    # large coordinates (pad scales with distance)
+    (7, 6000, 6.0, 60.0, False),    # more than 4096 small spheres: 32-slot groups (the coarsest size), 24 L2 nodes
 ])
 def test_accel_equals_brute_force_on_random_scenes(gpu, seed, n, spread, extent, ground):
     """Property test of the conservative slab test: on random sphere clouds and random cameras (inside and outside the
@@ -373,6 +374,43 @@ def test_accel_equals_brute_force_on_random_scenes(gpu, seed, n, spread, extent,
         i1, m1 = r.primary_hits(1, rt.RT_FLAG_ACCEL)
         assert np.array_equal(i0, i1) and np.array_equal(m0, m1)
         r.close()
+
+
+@pytest.mark.parametrize("name,n_random", [("d488", 0), ("s4096", 0), ("random", 900)])
+def test_accel_group_sizes_equal_brute_force(gpu, scene_factory, monkeypatch, name, n_random):
+    """build_accel picks the finest of 8 / 16 / 32 slots per group that fits the 32 x 8 fan-out; RT_ACCEL_GSHIFT forces a
+    coarser one.  Every size (a different kernel instantiation and image layout each) must reproduce brute force bit for bit,
+    and a finer size must evaluate fewer sphere tests."""
+    rt = gpu
+    w, h = 160, 90
+    if name == "random":
+        scene = _random_scene(rt, np.random.default_rng(11), n_random, 10.0, 12.0, True)
+        cam = rt.Camera((9.0, 1.5, 7.0), (0.0, 0.3, 0.0), 35.0, w / h, 11.0, 0.2)
+    else:
+        scene, _ = scene_factory(name)
+        cam = rt.scenes.default_camera(aspect=w / h)
+    monkeypatch.delenv("RT_ACCEL_GSHIFT", raising=False)
+    r = _renderer(rt, scene, cam, w, h)
+    r.reset_stats(); r.render(3, 50, 0)
+    ref, sref = r.read_hdr_sum(), r.stats()
+    ids_ref = r.primary_hits(1, 0)
+    r.close()
+    tests = {}
+    for g in (3, 4, 5):
+        monkeypatch.setenv("RT_ACCEL_GSHIFT", str(g))
+        r = _renderer(rt, scene, cam, w, h)              # rt_set_scene reads the override
+        r.reset_stats(); r.render(3, 50, rt.RT_FLAG_ACCEL)
+        b, sb = r.read_hdr_sum(), r.stats()
+        assert np.array_equal(ref, b, equal_nan=True), g
+        assert (sref.paths, sref.closest_rays, sref.shadow_rays) == (sb.paths, sb.closest_rays, sb.shadow_rays)
+        ids = r.primary_hits(1, rt.RT_FLAG_ACCEL)
+        assert np.array_equal(ids_ref[0], ids[0]) and np.array_equal(ids_ref[1], ids[1])
+        tests[g] = sb.sphere_tests
+        r.close()
+    if name == "s4096":
+        assert tests[3] == tests[4] > 0 and tests[4] < tests[5]     # 8 slots would need 512 groups: clamped to 16
+    else:
+        assert tests[3] < tests[4] < tests[5]
 
 
 def test_accel_empty_scene_and_limits(gpu):
