@@ -112,6 +112,18 @@ int rt_group_create(const int* devices, int n, int width, int height, rt_group**
         const ncclResult_t r = nccl_rt::CommInitAll(comms.data(), n, devs.data());
         if (r != ncclSuccess) { rt_group_destroy(g); return gfail(RT_ERR_NCCL, "ncclCommInitAll(%d devices) failed: %s", n, nccl_rt::GetErrorString(r)); }
         for (int i = 0; i < n; ++i) g->m[i].comm = comms[i];
+        // NCCL connects its transports at the first collective of a given size class (~0.3 s for 8 ranks in one process).  Pay
+        // that here, with the very reduce rt_group_render issues: the framebuffers were just cleared, so the sum is zero as well.
+        const size_t count = static_cast<size_t>(width) * height * 4;
+        void* root_buf = rt_hdr_device_ptr(g->m[0].ctx);
+        ncclResult_t wr = nccl_rt::GroupStart();
+        for (int i = 0; i < n && wr == ncclSuccess; ++i)
+            wr = nccl_rt::Reduce(rt_hdr_device_ptr(g->m[i].ctx), i == 0 ? root_buf : nullptr, count, ncclFloat, ncclSum, 0, g->m[i].comm,
+                                 static_cast<cudaStream_t>(rt_get_stream(g->m[i].ctx)));
+        const ncclResult_t we = nccl_rt::GroupEnd();
+        if (wr == ncclSuccess) wr = we;
+        if (wr != ncclSuccess) { rt_group_destroy(g); return gfail(RT_ERR_NCCL, "rt_group_create: warm-up ncclReduce failed: %s", nccl_rt::GetErrorString(wr)); }
+        for (int i = 0; i < n; ++i) { const int rc = rt_synchronize(g->m[i].ctx); if (rc != RT_OK) { forward(rc); rt_group_destroy(g); return rc; } }
     }
     *out = g;
     return RT_OK;
