@@ -75,10 +75,11 @@ __device__ __forceinline__ void stage_scene(const RenderParams& p, float4*& sA, 
 
 // Unshadowed DirectionalLight::Shade (light.cpp:20-40) for one light; the occlusion test is resolved by the
 // next fused pass (the shadow ray shares its origin with the scattered ray).
-__device__ __forceinline__ V3 direct_unshadowed(const RenderParams& p, const DevMat& m, V3 pos, V3 n, float u, float v, float n_dot_l) {
+// `tex` = texture_rgb(m, u, v), evaluated once per hit and shared with scatter().
+__device__ __forceinline__ V3 direct_unshadowed(const RenderParams& p, const DevMat& m, V3 pos, V3 n, V3 tex, float n_dot_l) {
     V3 albedo = mk3(0.f, 0.f, 0.f), f0 = mk3(0.04f, 0.04f, 0.04f);            // material.h:27-29,43-45,60-62
-    if (m.kind == 0) albedo = texture_rgb(m, u, v);
-    else if (m.kind == 1) f0 = texture_rgb(m, u, v);
+    if (m.kind == 0) albedo = tex;
+    else if (m.kind == 1) f0 = tex;
     const float s = m.smoothness;
     const V3 L = mk3(p.Lx, p.Ly, p.Lz);
     const V3 rin = mk3(p.lcx * n_dot_l, p.lcy * n_dot_l, p.lcz * n_dot_l);     // :27
@@ -95,18 +96,21 @@ __device__ __forceinline__ V3 direct_unshadowed(const RenderParams& p, const Dev
 }
 
 // Material::Scatter, material.cpp:20-164.  Returns false when the path ends here.
-__device__ __forceinline__ bool scatter(const DevMat& m, V3 d, V3 pos, V3 n, float u, float v,
+// The mirror direction normalize(reflect(d, n)) is what all three materials return on their reflecting branch (:35, :89, :155);
+// it is evaluated once in front of the material switch (the warp would otherwise run up to three copies of it per pass).
+__device__ __forceinline__ bool scatter(const DevMat& m, V3 d, V3 pos, V3 n, V3 tex,
                                         float xi, float u1, float u2, V3& atten, V3& out_d) {
+    const V3 mirror = normalize3(reflect3(d, n));
     if (m.kind == 0) {                                                         // DielectricOpaque
         const float ndv = dot3(neg3(d), n);
         if (!(ndv > 0.f)) return false;                                        // :22
         const float refl = schlick(0.04f, saturate1(ndv));                     // :25-27
         if (refl > xi) {                                                       // :29-30
             atten = mk3(1.f, 1.f, 1.f);
-            out_d = normalize3(reflect3(d, n));                                // :35
+            out_d = mirror;                                                    // :35
             return true;
         }
-        atten = texture_rgb(m, u, v);                                          // :41
+        atten = tex;                                                           // :41
         const V3 dir = hemisphere_from_u(u1, u2);                              // :44
         const V3 up = fabsf(n.x) < 0.5f ? mk3(1.f, 0.f, 0.f) : mk3(0.f, 1.f, 0.f);   // :50
         const V3 b1 = cross3(up, n);                                           // :51
@@ -117,8 +121,8 @@ __device__ __forceinline__ bool scatter(const DevMat& m, V3 d, V3 pos, V3 n, flo
     if (m.kind == 1) {                                                         // Metal: always reflects (alpha lane, :81-85)
         const float ndv = dot3(neg3(d), n);
         if (!(ndv > 0.f)) return false;                                        // :74
-        atten = texture_rgb(m, u, v);                                          // :87
-        out_d = normalize3(reflect3(d, n));                                    // :89
+        atten = tex;                                                           // :87
+        out_d = mirror;                                                        // :89
         return true;
     }
     atten = mk3(1.f, 1.f, 1.f);                                                // DielectricTransparent :114
@@ -129,7 +133,7 @@ __device__ __forceinline__ bool scatter(const DevMat& m, V3 d, V3 pos, V3 n, flo
     const V3 refr = refract3(d, outward, eta);                                 // :137
     const bool can_refract = (refr.x != 0.f) || (refr.y != 0.f) || (refr.z != 0.f);
     const float prob = can_refract ? fresnel_term(cos_i, m.ior) : 1.0f;        // :140-149
-    out_d = (prob > xi) ? normalize3(reflect3(d, n)) : normalize3(refr);       // :153-161
+    out_d = (prob > xi) ? mirror : normalize3(refr);                           // :153-161
     return true;
 }
 
@@ -263,6 +267,7 @@ __global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : RT_MAX
                     const V3 n = (pos - ctr) / radius;                                   // :62
                     const float tu = 0.5f * n.x + 0.5f, tv = 0.5f * n.z + 0.5f;          // :36-37
                     const DevMat m = p.mats[idx];
+                    const V3 tex = texture_rgb(m, tu, tv);                               // texture.cpp:8-33, once per hit
                     const bool cont = depth < p.max_depth;                               // spheres-app.cpp:247
                     V3 atten = mk3(0.f, 0.f, 0.f), nd = d;
                     bool scattered = false;
@@ -270,11 +275,11 @@ __global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : RT_MAX
                         float xi, u1, u2;
                         if constexpr (HALTON) draw_halton(m, p.sampler, d, n, xi, u1, u2);
                         else rng_counter(static_cast<uint32_t>(pix), p.first_sample + static_cast<u64>(s_cur), static_cast<uint32_t>(depth), p.seed, xi, u1, u2);
-                        scattered = scatter(m, d, pos, n, tu, tv, xi, u1, u2, atten, nd);      // :246
+                        scattered = scatter(m, d, pos, n, tex, xi, u1, u2, atten, nd);      // :246
                     }
                     if (has_light) {                                                     // :250
                         const float n_dot_l = saturate1(dot3(n, Ldir));                  // light.cpp:26
-                        if (n_dot_l > 0.f) { pend = T * direct_unshadowed(p, m, pos, n, tu, tv, n_dot_l); want_shadow = true; }
+                        if (n_dot_l > 0.f) { pend = T * direct_unshadowed(p, m, pos, n, tex, n_dot_l); want_shadow = true; }
                         else { ++n_shadow; ++n_skip; }   // facing away: radianceIn == 0 (light.cpp:27), so the term is 0 whether or not the
                                              // reference's shadow ray (:13-15) is occluded; the ray is counted, not traced
                     }

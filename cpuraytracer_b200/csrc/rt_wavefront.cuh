@@ -86,17 +86,18 @@ __global__ void __launch_bounds__(256) wf_shade_kernel(const RenderParams p, con
                     const V3 n = (pos - ctr) / radius;
                     const float tu = 0.5f * n.x + 0.5f, tv = 0.5f * n.z + 0.5f;
                     const DevMat m = p.mats[idx];
+                    const V3 tex = texture_rgb(m, tu, tv);
                     const bool cont = depth < p.max_depth;
                     V3 atten = mk3(0.f, 0.f, 0.f), nd = d;
                     bool scattered = false;
                     if (cont) {
                         float xi, u1, u2;
                         rng_counter(static_cast<uint32_t>(pix), p.first_sample + static_cast<u64>(s_cur), static_cast<uint32_t>(depth), p.seed, xi, u1, u2);
-                        scattered = scatter(m, d, pos, n, tu, tv, xi, u1, u2, atten, nd);
+                        scattered = scatter(m, d, pos, n, tex, xi, u1, u2, atten, nd);
                     }
                     if (has_light) {
                         const float n_dot_l = saturate1(dot3(n, Ldir));
-                        if (n_dot_l > 0.f) { pend = T * direct_unshadowed(p, m, pos, n, tu, tv, n_dot_l); want_shadow = true; }
+                        if (n_dot_l > 0.f) { pend = T * direct_unshadowed(p, m, pos, n, tex, n_dot_l); want_shadow = true; }
                         else { ++n_shadow; ++n_skip; }
                     }
                     o = pos;
