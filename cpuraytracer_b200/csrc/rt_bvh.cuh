@@ -122,7 +122,8 @@ __device__ __forceinline__ void cull_pair2(const CullRay2& r, const float4 A, co
 struct BoxRay { float ix, iy, iz, ax, ay, az, nx, ny, nz, fx, fy, fz; };
 __device__ __forceinline__ float safe_inv(float d) {
     const float dd = fabsf(d) < 1e-18f ? copysignf(1e-18f, d) : d;
-    return 1.0f / dd;
+    return div_rn(1.0f, dd);          // |dd| in [1e-18, ~1]: inside div_rn's range, so this is the correctly rounded 1/dd, without the
+                                      // range check and slow path nvcc attaches to `1.0f / dd`
 }
 __device__ __forceinline__ BoxRay box_ray(V3 o, float ix, float iy, float iz, float pad) {
     BoxRay r;
