@@ -141,7 +141,8 @@ __device__ __forceinline__ bool box_touched(const BoxRay& r, float cx, float cy,
     const float tnz = fmaf(-hz, r.az, fmaf(cz, r.iz, r.nz)), tfz = fmaf(hz, r.az, fmaf(cz, r.iz, r.fz));
     const float tn = fmaxf(fmaxf(tnx, tny), tnz);
     const float tf = fminf(fminf(tfx, tfy), tfz);
-    return tn <= tf && tf >= neg_t_slack;
+    return fmaxf(tn, neg_t_slack) <= tf;              // == (tn <= tf && tf >= neg_t_slack): no NaN reaches this point (finite boxes,
+                                                      // |inv| <= 1e18; an empty child has h = -1e30, i.e. tn = +inf, tf = -inf)
 }
 
 struct AccelCounters { uint32_t group_visits; };
@@ -179,11 +180,14 @@ __device__ __forceinline__ QueryResult fused_query_accel(const AccelSmem& s, con
     const float pad = 1.5f * fminf(E / (2.0f * a.r_min), sqrtf(E))
                     + 1.9073486328125e-06f * (fabsf(o.x) + fabsf(o.y) + fabsf(o.z) + a.c_max);      // 2^-19
     const float neg_t_slack = -1.52587890625e-05f * dmax;                                            // 2^-16
-    const BoxRay rc = box_ray(o, safe_inv(d.x), safe_inv(d.y), safe_inv(d.z), pad);
-    const BoxRay rs = box_ray(o, invL.x, invL.y, invL.z, pad);
-    const bool wc = want_closest, ws = want_shadow;
+    // a ray this lane does not ask for can never touch a box (near planes at +inf, far planes at -inf), so the box loops need no
+    // per-box masking by want_closest / want_shadow
+    BoxRay rc = box_ray(o, safe_inv(d.x), safe_inv(d.y), safe_inv(d.z), pad);
+    BoxRay rs = box_ray(o, invL.x, invL.y, invL.z, pad);
+    if (!want_closest) { rc.nx = __int_as_float(0x7f800000); rc.fx = __int_as_float(0xff800000); }
+    if (!want_shadow) { rs.nx = __int_as_float(0x7f800000); rs.fx = __int_as_float(0xff800000); }
 
-    // ---- T: L2 boxes, converged.  Both rays are tested without a branch (a lane that does not want a ray masks the answer).
+    // ---- T: L2 boxes, converged.  Both rays are tested without a branch (a ray the lane does not want touches nothing, see above).
     // With at most RT_ACCEL_FLAT_NODES L2 nodes (<= 1024 small spheres) their boxes are so large that nearly every ray touches
     // them: the level is skipped and every lane runs M over all nodes, converged and with broadcast loads. ----
     const bool flat = a.n2 <= RT_ACCEL_FLAT_NODES;
@@ -193,10 +197,10 @@ __device__ __forceinline__ QueryResult fused_query_accel(const AccelSmem& s, con
             const float4 b0 = s.top[2 * j], b1 = s.top[2 * j + 1];
             const bool hc = box_touched(rc, b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, neg_t_slack);
             const bool hs = box_touched(rs, b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, neg_t_slack);
-            if ((hc & wc) | (hs & ws)) m2 |= 1u << j;
+            if (hc | hs) m2 |= 1u << j;
         }
     }
-    if (!(wc | ws)) m2 = 0u;
+    if (!(want_closest | want_shadow)) m2 = 0u;
 
     // ---- M: group boxes of the touched L2 nodes ----
     uint32_t m2g = 0u;
@@ -213,7 +217,7 @@ __device__ __forceinline__ QueryResult fused_query_accel(const AccelSmem& s, con
             for (int k = 0; k < 4; ++k) {
                 const bool hc = box_touched(rc, cxa[k], cya[k], cza[k], hxa[k], hya[k], hza[k], neg_t_slack);
                 const bool hs = box_touched(rs, cxa[k], cya[k], cza[k], hxa[k], hya[k], hza[k], neg_t_slack);
-                if ((hc & wc) | (hs & ws)) byte |= 1u << (h * 4 + k);
+                if (hc | hs) byte |= 1u << (h * 4 + k);
             }
         }
         if (byte) {
