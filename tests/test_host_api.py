@@ -158,3 +158,19 @@ def test_image_sinks(rt, tmp_path):
     rt.write_pfm(q, hdr, 4)
     raw = open(q, "rb").read()
     assert raw.startswith(b"PF\n3 2\n-1.0\n") and np.frombuffer(raw[-72:], "<f4").tolist() == [1.0] * 18
+
+
+def test_bench_traffic_lookup_and_reference_arm_shape():
+    """bench.py's roofline.traffic comes from the committed ncu capture of the bench launch (profiles/traffic.json), keyed by
+    workload and query mode; a workload without a capture reports None instead of a guess."""
+    import importlib.util
+    import json
+    spec = importlib.util.spec_from_file_location("bench_mod", os.path.join(ROOT, "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    table = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+    for key in ("c3:brute", "c3:accel"):
+        wl, q = key.split(":")
+        assert bench._ncu_traffic(wl, q) == table[key]["bytes"] == table[key]["read"] + table[key]["write"]
+    assert bench._ncu_traffic("c4", "brute") is None
+    assert bench._ncu_traffic("nope", "brute") is None
