@@ -4,7 +4,8 @@
 // Brute force (rt_device.cuh, fused_query) stays the parity ground truth; this path must return the SAME bits:
 //   * the spheres are re-ordered on the host (rt_b200.cu, build_accel): "big" spheres first (radius > 4 x median -- the
 //     r = 1000 ground would bloat every box that contains it), then the rest in Morton order of their centres;
-//     32 consecutive slots form a GROUP (the unit of the candidate masks), 8 consecutive groups an L2 NODE;
+//     8, 16 or 32 consecutive slots (AccelParams::gshift, the finest size that fits the fan-out) form a GROUP (the unit of the
+//     candidate masks; the big spheres' groups always have 32), 8 consecutive groups an L2 NODE;
 //   * a group is visited when the closest ray or the shadow ray touches its (padded) bounding box; visited groups go
 //     through the SAME conservative FFMA2 discriminant cull as brute force, and every candidate through the SAME exact
 //     Sphere::Intersect restatement (sphere_exact), so an accepted hit has the reference's t bit for bit;
@@ -17,7 +18,7 @@
 //   T  top             converged loop over the n2 L2 boxes                       -> bit mask m2 of touched L2 nodes
 //   M  middle          per lane: pop an L2 node, test its 8 group boxes          -> one byte per L2 node in shared memory
 //   G  groups          the big spheres first (every lane, same addresses: broadcast LDS), then per lane: pop a touched group,
-//                      cull its 16 sphere pairs for both rays (pair order XOR-swizzled by the lane id so that the
+//                      cull its 4 / 8 / 16 sphere pairs for both rays (pair order XOR-swizzled by the lane id so that the
 //                      quarter-warps' LDS.128 hit 8 different bank groups)       -> candidate-mask entries
 //   E  exact           per lane: walk the entries, exact test per candidate
 #pragma once
@@ -30,7 +31,7 @@ struct AccelParams {
     const uint4* blob;       // device copy of the image
     int blob_bytes;          // multiple of 16
     int off_B, off_R, off_I, off_box, off_top;   // byte offsets of the sections (A starts at 0)
-    int n_pairs;             // sphere pairs in the image (big groups + small groups, each padded to 32 slots)
+    int n_pairs;             // sphere pairs in the image (big groups padded to 32 slots, small groups to 2^gshift)
     int n_big_groups;        // groups that are always culled
     int n_big_pairs;         // sphere pairs of the big groups that hold spheres (the rest of the last big group is padding)
     int n_groups;            // small groups (Morton order), 2^gshift slots each
