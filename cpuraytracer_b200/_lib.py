@@ -39,6 +39,14 @@ class CameraBasis(C.Structure):
                 ("image_origin", C.c_float * 3), ("aperture", C.c_float), ("focus", C.c_float)]
 
 
+class AccelImageInfo(C.Structure):
+    _fields_ = [("bytes", C.c_size_t), ("off_B", C.c_int32), ("off_R", C.c_int32), ("off_I", C.c_int32), ("off_box", C.c_int32),
+                ("off_top", C.c_int32), ("n_pairs", C.c_int32), ("n_big_groups", C.c_int32), ("n_big_pairs", C.c_int32),
+                ("n_groups", C.c_int32), ("group_slots", C.c_int32), ("n_l2_nodes", C.c_int32), ("node_floats", C.c_int32),
+                ("bound_center", C.c_float * 3), ("bound_radius", C.c_float), ("r_min", C.c_float), ("r_max", C.c_float),
+                ("c_max", C.c_float)]
+
+
 class Stats(C.Structure):
     _fields_ = [("paths", C.c_uint64), ("closest_rays", C.c_uint64), ("shadow_rays", C.c_uint64),
                 ("sphere_tests", C.c_uint64), ("passes", C.c_uint64), ("render_ms", C.c_double),
@@ -92,6 +100,7 @@ SYMBOLS = [
     ("rt_primary_hits", C.c_int, [_P, C.c_uint64, C.c_uint32, _P, _P, C.c_size_t]),
     ("rt_hdr_device_ptr", _P, [_P]),
     ("rt_hdr_bind_external", C.c_int, [_P, _P]),
+    ("rt_scene_accel_image", C.c_int, [_P, _P, C.c_size_t, C.POINTER(AccelImageInfo)]),
     ("rt_get_stats", C.c_int, [_P, C.POINTER(Stats)]),
     ("rt_stats_reset", C.c_int, [_P]),
     ("rt_build_info", C.c_char_p, []),

@@ -139,6 +139,15 @@ class Scene:
     def handle(self):
         return self._h
 
+    def accel_image(self):
+        """(info, image bytes) of the box hierarchy RT_FLAG_ACCEL stages for this scene (rt_scene_accel_image: host only, no
+        device needed); layout in include/rt_b200.h.  Raises RtError(RT_ERR_UNSUPPORTED) when the scene has no hierarchy."""
+        info = L.AccelImageInfo()
+        L.check(self._lib.rt_scene_accel_image(self._h, None, 0, C.byref(info)))
+        buf = np.zeros(info.bytes, dtype=np.uint8)
+        L.check(self._lib.rt_scene_accel_image(self._h, buf.ctypes.data_as(C.c_void_p), buf.nbytes, C.byref(info)))
+        return info, buf
+
     # -- low-level recorder (ids) --
     def add_texture(self, tex: Texture) -> int:
         key = id(tex)

@@ -306,12 +306,12 @@ template <int G> static const void* accel_primary_fn() { return reinterpret_cast
 static const void* accel_render_kernel(int gshift) { return gshift == 3 ? accel_render_fn<3>() : gshift == 4 ? accel_render_fn<4>() : accel_render_fn<5>(); }
 static const void* accel_primary_kernel(int gshift) { return gshift == 3 ? accel_primary_fn<3>() : gshift == 4 ? accel_primary_fn<4>() : accel_primary_fn<5>(); }
 
-static int build_accel(rt_context* c, const rt_scene* s) {
-    c->accel_ok = false; c->accel_why.clear();
-    rt::AccelParams& a = c->base.accel;
+// Host half of build_accel: the position-independent image and its section table (no CUDA call, no context), also reachable
+// through rt_scene_accel_image() so that the CPU tests can check its invariants.  false + `why` = hierarchy unavailable.
+static bool make_accel_image(const rt_scene* s, rt::AccelParams& a, std::vector<unsigned char>& img, std::string& why) {
     a = rt::AccelParams{};
     const int n = static_cast<int>(s->spheres.size());
-    if (n > 65000) { c->accel_why = "more than 65000 spheres (slot -> index map is 16 bit)"; return RT_OK; }
+    if (n > 65000) { why = "more than 65000 spheres (slot -> index map is 16 bit)"; return false; }
     // big spheres: radius > 4 x median (at most 64, the largest first)
     std::vector<float> radii(n);
     for (int i = 0; i < n; ++i) radii[i] = s->spheres[i].radius;
@@ -345,7 +345,7 @@ static int build_accel(rt_context* c, const rt_scene* s) {
     const int GS = 1 << gshift;
     const int n_groups = (static_cast<int>(small.size()) + GS - 1) / GS;
     const int n2 = (n_groups + 7) / 8;
-    if (n2 > 32) { c->accel_why = "too many small spheres for this group size (the L2 mask is one 32-bit word: at most 8192 with 32-slot groups)"; return RT_OK; }
+    if (n2 > 32) { why = "too many small spheres for this group size (the L2 mask is one 32-bit word: at most 8192 with 32-slot groups)"; return false; }
     const int small_base = n_big_groups * 32;
     const int n_slots = small_base + n_groups * GS;
     std::vector<int> slot_orig(std::max(n_slots, 1), -1);
@@ -360,7 +360,7 @@ static int build_accel(rt_context* c, const rt_scene* s) {
     const size_t off_box = align16(off_I + static_cast<size_t>(n_slots) * 2);
     const size_t off_top = off_box + static_cast<size_t>(n2) * RT_ACCEL_NODE_FLOATS * 4;
     const size_t total = std::max<size_t>(16, off_top + static_cast<size_t>(n2) * 32);
-    std::vector<unsigned char> img(total, 0);
+    img.assign(total, 0);
     float* A = reinterpret_cast<float*>(img.data() + off_A); float* B = reinterpret_cast<float*>(img.data() + off_B);
     float* R = reinterpret_cast<float*>(img.data() + off_R); uint16_t* I = reinterpret_cast<uint16_t*>(img.data() + off_I);
     float* BOX = reinterpret_cast<float*>(img.data() + off_box); float* TOP = reinterpret_cast<float*>(img.data() + off_top);
@@ -430,13 +430,24 @@ static int build_accel(rt_context* c, const rt_scene* s) {
         a.cs_radius = round_up(rad * (1.0 + 1e-6)); a.c_max = round_up(cmax);
         a.r_min = static_cast<float>(r_min); a.r_max = static_cast<float>(r_max);
     }
-    if (int r = dev_realloc(c->accel_blob, total / 16)) return r;
-    RT_CUDA(cudaMemcpyAsync(c->accel_blob, img.data(), total, cudaMemcpyHostToDevice, c->stream));
-    RT_CUDA(cudaStreamSynchronize(c->stream));
-    a.blob = c->accel_blob; a.blob_bytes = static_cast<int>(total);
+    a.blob = nullptr; a.blob_bytes = static_cast<int>(total);
     a.off_B = static_cast<int>(off_B); a.off_R = static_cast<int>(off_R); a.off_I = static_cast<int>(off_I);
     a.off_box = static_cast<int>(off_box); a.off_top = static_cast<int>(off_top);
     a.n_pairs = np; a.n_big_groups = n_big_groups; a.n_big_pairs = (static_cast<int>(big.size()) + 1) / 2; a.n_groups = n_groups; a.gshift = gshift; a.n2 = n2; a.gmask_words = std::max(1, (n2 + 3) / 4);
+    return true;
+}
+
+static int build_accel(rt_context* c, const rt_scene* s) {
+    c->accel_ok = false; c->accel_why.clear();
+    rt::AccelParams& a = c->base.accel;
+    std::vector<unsigned char> img;
+    if (!make_accel_image(s, a, img, c->accel_why)) return RT_OK;
+    const size_t total = img.size();
+    const int gshift = a.gshift;
+    if (int r = dev_realloc(c->accel_blob, total / 16)) return r;
+    RT_CUDA(cudaMemcpyAsync(c->accel_blob, img.data(), total, cudaMemcpyHostToDevice, c->stream));
+    RT_CUDA(cudaStreamSynchronize(c->stream));
+    a.blob = c->accel_blob;
     // CTA size: most resident warps per SM next to one image copy per CTA
     const int optin = static_cast<int>(c->prop.sharedMemPerBlockOptin);
     RT_CUDA(cudaFuncSetAttribute(accel_render_kernel(gshift), cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
@@ -893,6 +904,23 @@ int rt_primary_hits(rt_context* c, uint64_t sample, uint32_t flags, int32_t* sph
     if (sphere_idx) RT_CUDA(cudaMemcpyAsync(sphere_idx, c->ids, n * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
     if (material_id) RT_CUDA(cudaMemcpyAsync(material_id, c->mids, n * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
     RT_CUDA(cudaStreamSynchronize(c->stream));
+    return RT_OK;
+}
+int rt_scene_accel_image(const rt_scene* s, void* buf, size_t capacity, rt_accel_image_info* info) {
+    if (!s || !info) return fail(RT_ERR_INVALID_ARGUMENT, "rt_scene_accel_image: NULL argument");
+    rt::AccelParams a; std::vector<unsigned char> img; std::string why;
+    if (!make_accel_image(s, a, img, why)) return fail(RT_ERR_UNSUPPORTED, "rt_scene_accel_image: RT_FLAG_ACCEL unavailable for this scene: %s", why.c_str());
+    *info = rt_accel_image_info{};
+    info->bytes = img.size();
+    info->off_B = a.off_B; info->off_R = a.off_R; info->off_I = a.off_I; info->off_box = a.off_box; info->off_top = a.off_top;
+    info->n_pairs = a.n_pairs; info->n_big_groups = a.n_big_groups; info->n_big_pairs = a.n_big_pairs; info->n_groups = a.n_groups;
+    info->group_slots = 1 << a.gshift; info->n_l2_nodes = a.n2; info->node_floats = RT_ACCEL_NODE_FLOATS;
+    info->bound_center[0] = a.csx; info->bound_center[1] = a.csy; info->bound_center[2] = a.csz; info->bound_radius = a.cs_radius;
+    info->r_min = a.r_min; info->r_max = a.r_max; info->c_max = a.c_max;
+    if (buf) {
+        if (capacity < img.size()) return fail(RT_ERR_INVALID_ARGUMENT, "rt_scene_accel_image: buffer of %zu bytes, image needs %zu", capacity, img.size());
+        std::memcpy(buf, img.data(), img.size());
+    }
     return RT_OK;
 }
 int rt_get_stats(rt_context* c, rt_stats* out) {

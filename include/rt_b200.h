@@ -153,6 +153,24 @@ RT_API int  rt_resolve_ldr(rt_context* ctx, uint64_t sample_count, uint32_t* bgr
 /* Primary-hit id buffers for frame `sample`: sphere index (-1 = miss) and material id (RT_MAT_*). */
 RT_API int  rt_primary_hits(rt_context* ctx, uint64_t sample, uint32_t flags, int32_t* sphere_idx, int32_t* material_id, size_t n_pixels);
 
+/* ---- inspection: the hierarchy image RT_FLAG_ACCEL stages into shared memory ----
+ * What rt_set_scene builds in place of the reference's BvhNode tree (ray-tracing.cpp:107-167): host-only, needs no device.
+ * Layout (all offsets in bytes from the start of the image; "slot" = position of a sphere in the re-ordered list, two slots = one pair):
+ *   [0, off_B)        float4 per pair (cx0, cx1, cy0, cy1)         [off_B, off_R)   float4 per pair (cz0, cz1, w0, w1)
+ *   [off_R, off_I)    float radius per slot                         [off_I, off_box) uint16 original sphere index per slot (0xFFFF = padding)
+ *   [off_box, off_top) per L2 node `node_floats` floats: 8 children x (cx, cy, cz, hx, hy, hz) SoA (centre / half extent; empty: h = -1e30)
+ *   [off_top, bytes)  per L2 node 8 floats (cx, cy, cz, hx, hy, hz, -, -)
+ * Slots [0, 32 n_big_groups) hold the big spheres, then n_groups small groups of group_slots slots in Morton order; 8 groups = one L2 node. */
+typedef struct rt_accel_image_info {
+    size_t  bytes;
+    int32_t off_B, off_R, off_I, off_box, off_top;
+    int32_t n_pairs, n_big_groups, n_big_pairs, n_groups, group_slots, n_l2_nodes, node_floats;
+    float   bound_center[3], bound_radius;     /* sphere around all small spheres (pad of the slab test) */
+    float   r_min, r_max, c_max;               /* smallest / largest small-sphere radius, largest |coordinate| of a box face */
+} rt_accel_image_info;
+/* Fills `info`; copies the image into buf when buf != NULL (capacity >= info->bytes).  RT_ERR_UNSUPPORTED when the scene has no hierarchy. */
+RT_API int  rt_scene_accel_image(const rt_scene* scene, void* buf, size_t capacity, rt_accel_image_info* info);
+
 /* ---- interop / instrumentation ---- */
 RT_API void* rt_hdr_device_ptr(rt_context* ctx);                   /* float4[W*H] in HBM (e.g. for an NCCL reduce) */
 RT_API int  rt_hdr_bind_external(rt_context* ctx, void* device_ptr); /* render into a caller-owned device buffer (NULL = own buffer) */

@@ -174,3 +174,104 @@ def test_bench_traffic_lookup_and_reference_arm_shape():
         assert bench._ncu_traffic(wl, q) == table[key]["bytes"] == table[key]["read"] + table[key]["write"]
     assert bench._ncu_traffic("c4", "brute") is None
     assert bench._ncu_traffic("nope", "brute") is None
+
+
+# ---------------------------------------------------------------- RT_FLAG_ACCEL: invariants of the hierarchy image (host only)
+def _accel_sections(info, img):
+    f32 = img.view(np.float32)
+    n_slots = 2 * info.n_pairs
+    A = f32[: info.off_B // 4][: 4 * info.n_pairs].reshape(-1, 4)
+    B = f32[info.off_B // 4: info.off_B // 4 + 4 * info.n_pairs].reshape(-1, 4)
+    R = f32[info.off_R // 4: info.off_R // 4 + n_slots]
+    I = img[info.off_I: info.off_I + 2 * n_slots].view(np.uint16)
+    box = f32[info.off_box // 4: info.off_top // 4].reshape(info.n_l2_nodes, info.node_floats)
+    top = f32[info.off_top // 4: info.off_top // 4 + 8 * info.n_l2_nodes].reshape(info.n_l2_nodes, 8)
+    slot = np.arange(n_slots)
+    cx, cy = A[slot >> 1, slot & 1], A[slot >> 1, 2 + (slot & 1)]
+    cz, w = B[slot >> 1, slot & 1], B[slot >> 1, 2 + (slot & 1)]
+    return cx, cy, cz, w, R, I, box, top
+
+
+def _random_flat_scene(rt, seed, n, ground):
+    rng = np.random.default_rng(seed)
+    s = rt.Scene()
+    mat = rt.DielectricOpaque(rt.ConstTexture(rt.XMCOLOR(0.5, 0.5, 0.5)), 16.0)
+    if ground:
+        s.add(rt.Sphere((0.0, -1000.0, 0.0), 1000.0, mat))
+    for _ in range(n):
+        r = float(0.05 * 8.0 ** rng.uniform(0, 1))
+        c = rng.uniform(-30, 30, 3)
+        s.add(rt.Sphere(tuple(float(x) for x in c), r, mat))
+    s.set_sky(rt.Emissive(8000.0, rt.ConstTexture(rt.XMCOLOR(0.85, 0.91, 0.98))))
+    return s
+
+
+@pytest.mark.parametrize("which,expect_slots", [("d488", 8), ("s4096", 16), ("random600", 8), ("random6000", 32)])
+def test_accel_image_invariants(rt, monkeypatch, which, expect_slots):
+    """What makes RT_FLAG_ACCEL equal to brute force is decided on the host: every sphere sits in exactly one slot with the
+    same cull constants as the brute-force arrays, and every box contains the spheres below it, rounded outward."""
+    monkeypatch.delenv("RT_ACCEL_GSHIFT", raising=False)
+    if which.startswith("random"):
+        scene = _random_flat_scene(rt, 5, int(which[6:]), ground=True)
+    else:
+        scene = rt.scenes.NAMED[which]()
+    sp = scene.export().spheres
+    centres = np.stack([sp["cx"], sp["cy"], sp["cz"]], 1).astype(np.float64)
+    radii = sp["radius"].astype(np.float64)
+    n = len(radii)
+    info, img = scene.accel_image()
+    assert info.group_slots == expect_slots and info.bytes == img.nbytes and info.bytes % 16 == 0 and info.off_B % 256 == 0
+    assert info.n_groups <= 256 and info.n_l2_nodes == (info.n_groups + 7) // 8 <= 32
+    cx, cy, cz, w, R, I, box, top = _accel_sections(info, img)
+    used = I != 0xFFFF
+    assert sorted(I[used].tolist()) == list(range(n))                                  # a permutation of the scene
+    o = I[used].astype(np.int64)
+    assert np.array_equal(np.stack([cx, cy, cz], 1)[used], centres[o].astype(np.float32)) and np.array_equal(R[used], radii[o].astype(np.float32))
+    k = 2.0 ** -16
+    cc, r2 = (centres[o] ** 2).sum(1), radii[o] ** 2
+    assert np.array_equal(w[used], (r2 - cc + k * (cc + r2)).astype(np.float32))       # same -c' term as the brute-force arrays
+    assert np.all(w[~used] == np.float32(-1.0e30))                                     # padding can never be a candidate
+    n_big_slots = 32 * info.n_big_groups
+    big = I[:n_big_slots][I[:n_big_slots] != 0xFFFF]
+    small_slots = np.arange(n_big_slots, 2 * info.n_pairs)
+    small = I[small_slots]
+    assert len(big) + int((small != 0xFFFF).sum()) == n
+    if len(big) and (small != 0xFFFF).any():
+        assert radii[big].min() > radii[small[small != 0xFFFF]].max()                  # big = the largest radii
+    # boxes: group box and node box contain the spheres below them (centre / half extent, rounded outward)
+    gs = info.group_slots
+    for g in range(info.n_groups):
+        j2, kk = divmod(g, 8)
+        c = box[j2, [kk, 8 + kk, 16 + kk]].astype(np.float64)
+        h = box[j2, [24 + kk, 32 + kk, 40 + kk]].astype(np.float64)
+        members = small[g * gs:(g + 1) * gs]
+        members = members[members != 0xFFFF].astype(np.int64)
+        assert len(members) > 0
+        lo, hi = (centres[members] - radii[members, None]).min(0), (centres[members] + radii[members, None]).max(0)
+        assert np.all(c - h <= lo) and np.all(c + h >= hi), g
+        tc, th = top[j2, 0:3].astype(np.float64), top[j2, 3:6].astype(np.float64)     # the node box must hold the SPHERES below it (each
+        assert np.all(tc - th <= lo) and np.all(tc + th >= hi), g                      # level is rounded outward from the exact union on its own)
+    for g in range(info.n_groups, 8 * info.n_l2_nodes):                                # children past the last group are empty
+        j2, kk = divmod(g, 8)
+        assert np.all(box[j2, [24 + kk, 32 + kk, 40 + kk]] == np.float32(-1.0e30))
+    sm = small[small != 0xFFFF].astype(np.int64)
+    if len(sm):
+        bc = np.asarray(list(info.bound_center), np.float64)
+        assert np.all(np.linalg.norm(centres[sm] - bc, axis=1) + radii[sm] <= info.bound_radius)
+        assert info.r_min == np.float32(radii[sm].min()) and info.r_max == np.float32(radii[sm].max())
+        assert info.c_max >= np.abs(np.concatenate([centres[sm] - radii[sm, None], centres[sm] + radii[sm, None]])).max()
+
+
+def test_accel_image_group_size_override_and_limits(rt, monkeypatch):
+    scene = rt.scenes.NAMED["d488"]()
+    slots = {}
+    for g in (3, 4, 5):
+        monkeypatch.setenv("RT_ACCEL_GSHIFT", str(g))
+        info, _ = scene.accel_image()
+        slots[g] = (info.group_slots, info.n_groups)
+    assert slots == {3: (8, 61), 4: (16, 31), 5: (32, 16)}
+    monkeypatch.delenv("RT_ACCEL_GSHIFT")
+    too_many = _random_flat_scene(rt, 9, 8300, ground=False)                          # > 8192 small spheres: no hierarchy
+    with pytest.raises(rt.RtError) as e:
+        too_many.accel_image()
+    assert e.value.code == 5                                                           # RT_ERR_UNSUPPORTED
