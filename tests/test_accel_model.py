@@ -1,0 +1,125 @@
+"""CPU model of the two conservative filters in front of the exact ray-sphere test (no GPU): a numpy restatement, in binary32,
+of the packed discriminant cull (cpuraytracer_b200/csrc/rt_device.cuh cull_pair / rt_bvh.cuh cull_pair2) and of the padded slab
+test of RT_FLAG_ACCEL (rt_bvh.cuh box_ray / box_touched), run over the hierarchy image the library builds on the host
+(rt_scene_accel_image).  Property checked: whatever the exact test -- Sphere::Intersect in the reference's operation order,
+ray-tracing.cpp:42-84 -- accepts is never filtered out, for rays that start on sphere surfaces, inside spheres, far away and
+along the axes.  The GPU suite checks the kernels themselves (tests/test_gpu_parity.py::test_accel_*, test_cull_is_result_neutral);
+this file pins the arithmetic they are built from."""
+import numpy as np
+import pytest
+
+from test_host_api import _accel_sections, _random_flat_scene
+
+f32 = np.float32
+
+
+def fma(a, b, c):
+    """binary32 fused multiply-add (the product of two binary32 numbers is exact in binary64)"""
+    return (np.asarray(a, np.float64) * np.asarray(b, np.float64) + np.asarray(c, np.float64)).astype(f32)
+
+
+def exact_accepts(o, d, cx, cy, cz, r):
+    """Sphere::Intersect, reference operation order, one binary32 rounding per operation.  o, d: (R,3); spheres: (N,) -> (R,N) bool"""
+    ocx, ocy, ocz = o[:, None, 0] - cx[None], o[:, None, 1] - cy[None], o[:, None, 2] - cz[None]
+    dx, dy, dz = d[:, None, 0], d[:, None, 1], d[:, None, 2]
+    a = ((dx * dx + dy * dy) + dz * dz).astype(f32)
+    b = ((ocx * dx + ocy * dy) + ocz * dz).astype(f32)
+    c = (((ocx * ocx + ocy * ocy) + ocz * ocz) - (r * r)[None]).astype(f32)
+    disc = (b * b - a * c).astype(f32)
+    with np.errstate(invalid="ignore"):
+        sq = np.sqrt(np.where(disc > 0, disc, f32(0))).astype(f32)
+        t0, t1 = ((-b - sq) / a).astype(f32), ((-b + sq) / a).astype(f32)
+    return (disc > 0) & ((t0 > f32(0.001)) | (t1 > f32(0.001)))
+
+
+def cull_keeps(o, d, cx, cy, cz, w):
+    """sign of the conservative discriminant, the fma chain of cull_pair2 (one ray)"""
+    ox, oy, oz = (o[:, None, k] for k in range(3))
+    dx, dy, dz = (d[:, None, k] for k in range(3))
+    oo = fma(ox, ox, fma(oy, oy, (oz * oz).astype(f32)))
+    noo = fma(f32(2.0 ** -16), oo, -oo)
+    od = fma(ox, dx, fma(oy, dy, (oz * dz).astype(f32)))
+    nc2 = (w[None] + noo).astype(f32)
+    nc2 = fma((oz + oz).astype(f32), cz[None], nc2); nc2 = fma((oy + oy).astype(f32), cy[None], nc2); nc2 = fma((ox + ox).astype(f32), cx[None], nc2)
+    b1 = fma(-dz, cz[None], od); b1 = fma(-dy, cy[None], b1); b1 = fma(-dx, cx[None], b1)
+    d1 = fma(b1, b1, nc2)
+    return ~np.signbit(d1)
+
+
+def slab_touched(o, d, info, bc, bh):
+    """box_ray + box_touched for rays (R,3) against boxes (M,3) centre / half extent -> (R,M) bool"""
+    cs = np.asarray(list(info.bound_center), f32)
+    dc = (o - cs[None]).astype(f32)
+    dmax = (np.sqrt(fma(dc[:, 0], dc[:, 0], fma(dc[:, 1], dc[:, 1], (dc[:, 2] * dc[:, 2]).astype(f32)))).astype(f32) + f32(info.bound_radius)).astype(f32)
+    E = (f32(2.0 ** -18) * fma(dmax, dmax, f32(info.r_max) * f32(info.r_max))).astype(f32)
+    pad = ((f32(1.5) * np.minimum((E / (f32(2.0) * f32(info.r_min))).astype(f32), np.sqrt(E).astype(f32))).astype(f32)
+           + (f32(2.0 ** -19) * (((np.abs(o[:, 0]) + np.abs(o[:, 1])).astype(f32) + np.abs(o[:, 2])).astype(f32) + f32(info.c_max)).astype(f32)).astype(f32)).astype(f32)
+    nts = (f32(-(2.0 ** -16)) * dmax).astype(f32)
+    dd = np.where(np.abs(d) < f32(1e-18), np.copysign(f32(1e-18), d), d).astype(f32)
+    inv = (f32(1.0) / dd).astype(f32)
+    ax = np.abs(inv)
+    no = (-(o * inv)).astype(f32)
+    ex = (pad[:, None] * ax).astype(f32)
+    n, f = (no - ex).astype(f32), (no + ex).astype(f32)
+    tn = np.full((o.shape[0], bc.shape[0]), -np.inf, f32)
+    tf = np.full((o.shape[0], bc.shape[0]), np.inf, f32)
+    for k in range(3):
+        m_n = fma(bc[None, :, k], inv[:, None, k], n[:, None, k])
+        m_f = fma(bc[None, :, k], inv[:, None, k], f[:, None, k])
+        tn = np.maximum(tn, fma(-bh[None, :, k], ax[:, None, k], m_n))
+        tf = np.minimum(tf, fma(bh[None, :, k], ax[:, None, k], m_f))
+    return np.maximum(tn, nts[:, None]) <= tf
+
+
+def _rays(rng, centres, radii, n_rays):
+    """origins on sphere surfaces (as every bounce ray and shadow ray has), inside spheres, inside the field, far away; random and
+    axis-aligned directions"""
+    n = len(radii)
+    pick = rng.integers(0, n, n_rays)
+    u = rng.normal(size=(n_rays, 3)); u /= np.linalg.norm(u, axis=1, keepdims=True)
+    on = centres[pick] + radii[pick, None] * u
+    inside = centres[pick] + 0.5 * radii[pick, None] * u
+    lo, hi = centres.min(0), centres.max(0)
+    field = rng.uniform(lo - 1, hi + 1, (n_rays, 3))
+    far = field * rng.choice([3.0, 30.0, 300.0], (n_rays, 1))
+    o = np.concatenate([on, inside, field, far]).astype(f32)
+    d = rng.normal(size=(len(o), 3)); d /= np.linalg.norm(d, axis=1, keepdims=True)
+    axis = rng.integers(0, 3, len(o) // 8)
+    d[: len(axis)] = 0.0
+    d[np.arange(len(axis)), axis] = rng.choice([-1.0, 1.0], len(axis))
+    aim = rng.integers(0, n, len(o) // 2)                            # half of the rays aimed at (near) a sphere: plenty of hits and grazes
+    tgt = centres[aim] + radii[aim, None] * rng.uniform(-1.05, 1.05, (len(aim), 3))
+    v = tgt - o[len(o) // 2:].astype(np.float64)
+    d[len(o) // 2:] = v / np.maximum(np.linalg.norm(v, axis=1, keepdims=True), 1e-30)
+    return o, d.astype(f32)
+
+
+@pytest.mark.parametrize("which", ["d488", "random600", "s4096"])
+def test_filters_never_drop_what_the_exact_test_accepts(rt, monkeypatch, which):
+    monkeypatch.delenv("RT_ACCEL_GSHIFT", raising=False)
+    scene = _random_flat_scene(rt, 21, 600, ground=True) if which == "random600" else rt.scenes.NAMED[which]()
+    info, img = scene.accel_image()
+    cx, cy, cz, w, R, I, box, top = _accel_sections(info, img)
+    used = I != 0xFFFF
+    rng = np.random.default_rng(3)
+    centres = np.stack([cx, cy, cz], 1)[used].astype(np.float64)
+    o, d = _rays(rng, centres, R[used].astype(np.float64), 300 if which == "s4096" else 600)
+    acc = exact_accepts(o, d, cx, cy, cz, R) & used[None]            # (rays, slots)
+    assert acc.sum() > 2 * len(o) // 3                                 # the sample really exercises hits
+    keep = cull_keeps(o, d, cx, cy, cz, w)
+    assert not np.any(acc & ~keep), "the discriminant cull dropped an accepted sphere"
+    # group boxes / L2 boxes of the small spheres
+    gs, first = info.group_slots, 32 * info.n_big_groups
+    g_of_slot = (np.arange(2 * info.n_pairs) - first) // gs
+    gi = np.arange(info.n_groups)
+    bc = np.stack([box[gi // 8, a * 8 + gi % 8] for a in range(3)], 1)
+    bh = np.stack([box[gi // 8, 24 + a * 8 + gi % 8] for a in range(3)], 1)
+    touched = slab_touched(o, d, info, bc, bh)                        # (rays, groups)
+    tt = slab_touched(o, d, info, top[:, 0:3], top[:, 3:6])           # (rays, L2 nodes)
+    small = np.arange(2 * info.n_pairs) >= first
+    rr, ss = np.nonzero(acc & small[None])
+    assert len(rr) > 0
+    assert np.all(touched[rr, g_of_slot[ss]]), "a group box was skipped although the exact test accepts one of its spheres"
+    assert np.all(tt[rr, g_of_slot[ss] // 8]), "an L2 box was skipped although the exact test accepts one of its spheres"
+    # the boxes do filter: far fewer than all (ray, group) pairs are touched
+    assert touched.mean() < 0.5
