@@ -84,13 +84,25 @@ def _rays(rng, centres, radii, n_rays):
     far = field * rng.choice([3.0, 30.0, 300.0], (n_rays, 1))
     o = np.concatenate([on, inside, field, far]).astype(f32)
     d = rng.normal(size=(len(o), 3)); d /= np.linalg.norm(d, axis=1, keepdims=True)
-    axis = rng.integers(0, 3, len(o) // 8)
-    d[: len(axis)] = 0.0
-    d[np.arange(len(axis)), axis] = rng.choice([-1.0, 1.0], len(axis))
-    aim = rng.integers(0, n, len(o) // 2)                            # half of the rays aimed at (near) a sphere: plenty of hits and grazes
+    # the critical family for the pad: rays that graze a sphere at (almost) the point where it touches its own bounding box,
+    # travelling inside that face of the box
+    m = n_rays
+    pk, axis, sign = rng.integers(0, n, m), rng.integers(0, 3, m), rng.choice([-1.0, 1.0], m)
+    depth = rng.choice([0.0, 1e-7, 1e-6, 1e-5, 1e-3], m)
+    e = np.zeros((m, 3)); e[np.arange(m), axis] = sign
+    p = centres[pk] + radii[pk, None] * (1.0 - depth[:, None]) * e
+    t = rng.normal(size=(m, 3)); t -= (t * e).sum(1, keepdims=True) * e; t /= np.linalg.norm(t, axis=1, keepdims=True)
+    go = (p - rng.uniform(0.5, 50.0, (m, 1)) * t).astype(f32)
+    gd = (p - go.astype(np.float64)); gd /= np.linalg.norm(gd, axis=1, keepdims=True)
+    o = np.concatenate([o, go]); d = np.concatenate([d, gd])
+    n4 = 4 * n_rays                                                  # the first four families get axis-aligned and aimed directions
+    ax = rng.integers(0, 3, n4 // 8)
+    d[: len(ax)] = 0.0
+    d[np.arange(len(ax)), ax] = rng.choice([-1.0, 1.0], len(ax))
+    aim = rng.integers(0, n, n4 // 2)                                # half of them aimed at (near) a sphere: plenty of hits and grazes
     tgt = centres[aim] + radii[aim, None] * rng.uniform(-1.05, 1.05, (len(aim), 3))
-    v = tgt - o[len(o) // 2:].astype(np.float64)
-    d[len(o) // 2:] = v / np.maximum(np.linalg.norm(v, axis=1, keepdims=True), 1e-30)
+    v = tgt - o[n4 // 2: n4].astype(np.float64)
+    d[n4 // 2: n4] = v / np.maximum(np.linalg.norm(v, axis=1, keepdims=True), 1e-30)
     return o, d.astype(f32)
 
 
