@@ -282,7 +282,13 @@ template <class T> static int dev_realloc(T*& p, size_t n) {
 }
 static size_t scene_smem_bytes(int n_pad) { return static_cast<size_t>(n_pad / 2) * 40u + static_cast<size_t>(n_pad) * 4u; }
 // scene arrays + the per-thread candidate lists (2 lists x RT_LIST_CAP words), see stage_scene()
-static size_t cta_smem_bytes(int n_pad, int tpb) { return scene_smem_bytes(n_pad) + static_cast<size_t>(tpb) * 2u * RT_LIST_CAP * 4u; }
+static size_t cta_smem_bytes(int n_pad, int tpb) {
+    size_t b = scene_smem_bytes(n_pad) + static_cast<size_t>(tpb) * 2u * RT_LIST_CAP * 4u;
+#if RT_FLAT_EXACT
+    b += static_cast<size_t>((tpb + 31) / 32) * RT_WQ_BYTES_PER_WARP;       // per-warp candidate queue of the exact-test phase
+#endif
+    return b;
+}
 
 // ------------------------------------------------------------------------------------------------
 // RT_FLAG_ACCEL: host build of the box hierarchy image (layout + conservativeness argument: rt_bvh.cuh).

@@ -72,6 +72,18 @@ __device__ __forceinline__ void stage_scene(const RenderParams& p, float4*& sA, 
     for (int i = threadIdx.x; i < 2 * np; i += blockDim.x) sR[i] = p.radius[i];
     __syncthreads();
 }
+#if RT_FLAT_EXACT
+// This warp's queue, behind the candidate lists: [best keys 32 x 8 B][tasks RT_WQ_CAP x 4 B][occlusion word, 8 B] per warp.
+__device__ __forceinline__ WarpQueue warp_queue(const uint32_t* lists_col0) {
+    unsigned char* base = reinterpret_cast<unsigned char*>(const_cast<uint32_t*>(lists_col0) + 2 * RT_LIST_CAP * blockDim.x)
+                        + static_cast<size_t>(threadIdx.x >> 5) * RT_WQ_BYTES_PER_WARP;
+    WarpQueue q;
+    q.best = reinterpret_cast<u64*>(base);
+    q.tasks = reinterpret_cast<uint32_t*>(base + 32 * 8);
+    q.occ = reinterpret_cast<uint32_t*>(base + 32 * 8 + RT_WQ_CAP * 4);
+    return q;
+}
+#endif
 
 // Unshadowed DirectionalLight::Shade (light.cpp:20-40) for one light; the occlusion test is resolved by the
 // next fused pass (the shadow ray shares its origin with the scattered ray).
@@ -189,6 +201,10 @@ __global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : RT_MAX
         sA = const_cast<float4*>(av.sA); sB = const_cast<float4*>(av.sB); sR = const_cast<float*>(av.sR);
     } else stage_scene(p, sA, sB, sC, sR, lists, smem);
     const int lstride = static_cast<int>(blockDim.x);
+    WarpQueue wq{nullptr, nullptr, nullptr};
+#if RT_FLAT_EXACT
+    if constexpr (MODE == MODE_CULL) wq = warp_queue(lists - threadIdx.x);
+#endif
     const V3 invL = mk3(p.iLx, p.iLy, p.iLz);
     AccelCounters acnt; acnt.group_visits = 0u;
 
@@ -246,7 +262,7 @@ __global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : RT_MAX
         // ---- K2+K3: fused closest-hit / shadow query over every sphere ----
         QueryResult q;
         if constexpr (MODE == MODE_ACCEL) q = fused_query_accel<GSHIFT>(av, p.accel, lstride, o, d, Ldir, invL, active && want_closest, active && want_shadow, acnt);
-        else q = fused_query<MODE == MODE_NO_CULL>(sA, sB, sC, sR, lists, lstride, p.n_groups, p.n_spheres, o, d, Ldir, active && want_closest, active && want_shadow);
+        else q = fused_query<MODE == MODE_NO_CULL>(sA, sB, sC, sR, lists, lstride, p.n_groups, p.n_spheres, o, d, Ldir, active && want_closest, active && want_shadow, wq);
         ++n_pass;
 
         // ---- K4: integrate ----
