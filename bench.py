@@ -59,59 +59,77 @@ def parse_args():
 
 
 # ------------------------------------------------------------------------------------------------ CPU arm (oracle)
-def oracle_setup(workload):
-    """Scene + camera of the workload as flat arrays for the oracle.  The flat scene comes from the product's host
-    recorder (pure host code); the oracle is the thing timed here, never the other way round."""
-    import cpuraytracer_b200 as rt
-    from oracle import orc
-    scene_name, w, h, depth, _, _ = WORKLOADS[workload]
-    scene = rt.scenes.NAMED[scene_name]()
-    cam = rt.scenes.default_camera(aspect=w / h)
-    osc = orc.Scene.from_flat(scene.export())
-    cp = orc.camera_params(cam.origin, cam.look_at, cam.vertical_fov, cam.aspect_ratio, cam.focal_length, cam.aperture)
-    return orc, osc, cp, (w, h, depth)
+# This arm never imports cpuraytracer_b200 and never maps librt_b200.so: its scenes are the committed oracle/scenes/*.rtsc
+# (frozen copies of the named synthetic scenes; tests/test_host_api.py checks them against the product's recorder).
+class CpuArm:
+    """The reference's CPU implementation of the path on all host threads.  kind "reference": oracle/_ref -- the reference's
+    OWN common-lib sources compiled unmodified (g++ -O2, SSE2 baseline) + the headless DrawBitmap driver, ONE persistent world
+    (scene, BVH, per-material Halton counters, worker pool) across frames as in the reference.  kind "port": the oracle's
+    restatement in the reference's configuration (atomic Halton counters + BVH + recursive integrator)."""
 
+    def __init__(self, workload):
+        import numpy as np
+        from oracle import orc
+        self.orc, self.np = orc, np
+        scene_name, self.w, self.h, self.depth, _, _ = WORKLOADS[workload]
+        self.osc = orc.frozen_scene(scene_name)
+        self.cp = orc.default_camera_params(self.w / self.h)
+        self.hdr = np.zeros((self.h, self.w, 4), np.float32)
+        self.frame = 0
+        self.world = orc.RefWorld(self.osc, self.cp) if orc.load_ref() is not None else None
+        self.kind = "reference" if self.world is not None else "port"
+        self.threads = self.world.threads if self.world is not None else (os.cpu_count() or 1)
+        self.build = (orc.load_ref().ref_build_info() if self.world is not None else orc.load().orc_build_info()).decode()
 
-def oracle_reference_cfg(orc, w, h, depth, first, spp):
-    """The reference's configuration: shared atomic Halton counters (material.h:34,50-51,67), BVH
-    (ray-tracing.cpp:107-214), recursive GetHitColor (spheres-app.cpp:238-257), all hardware threads."""
-    return orc.config(w, h, spp=spp, max_depth=depth, first_sample=first, rng_mode=orc.RNG_HALTON,
-                      accel=orc.ACCEL_BVH, integrator=orc.INTEGRATOR_RECURSIVE, threads=0)
+    def frames(self, n=1, flags=0):
+        """n x DrawBitmap (1 spp over every pixel each), continuing the sample count and the sampler state."""
+        orc = self.orc
+        first = self.frame + 1
+        self.frame += n
+        if self.world is not None:
+            _, st = self.world.render(orc.config(self.w, self.h, spp=n, max_depth=self.depth, first_sample=first, flags=flags), self.hdr)
+        else:
+            _, st = orc.render(self.osc, self.cp, orc.config(self.w, self.h, spp=n, max_depth=self.depth, first_sample=first, rng_mode=orc.RNG_HALTON,
+                                                             accel=orc.ACCEL_BVH, integrator=orc.INTEGRATOR_RECURSIVE, threads=0), self.hdr)
+        return st
 
+    def describe(self):
+        return {"cores": self.threads, "kind": self.kind, "threads": self.threads, "host_cpus": os.cpu_count(), "build": self.build,
+                "compiler_flags": "g++ -O2 -std=c++17 -ffp-contract=off -fno-fast-math (x86-64 SSE2 baseline = /arch:SSE2, common-lib.vcxproj:72)",
+                "counters": "per-thread (no shared cache line per ray)", "world": "persistent across frames (scene, BVH, Halton indices, worker pool)",
+                "schedule": "rows handed to a persistent pool, primary ray generated by the tracing worker (kinder to the CPU than the "
+                            "reference's serial GenerateRays; that structure is timed under 'drawbitmap_structure')"}
 
-def cpu_frame(orc, osc, cp, w, h, depth, frame, hdr):
-    """One DrawBitmap (1 spp over every pixel) on all host threads.  Prefers oracle/_ref -- the reference's OWN common-lib
-    sources compiled headless against the DirectXMath stand-in (kind "reference"); falls back to the oracle port in the
-    reference's configuration (atomic Halton counters + BVH + recursive integrator; kind "port")."""
-    if orc.load_ref() is not None:
-        _, st = orc.ref_render(osc, cp, orc.config(w, h, spp=1, max_depth=depth, first_sample=frame, threads=0), hdr)
-        return st, "reference"
-    _, st = orc.render(osc, cp, oracle_reference_cfg(orc, w, h, depth, frame, 1), hdr)
-    return st, "port"
-
-
-CPU_NOTE = {"reference": "reference's own camera/light/material/quasi-random/ray-tracing/texture .cpp compiled unmodified (g++ -O2, SSE2, "
-                         "DirectXMath stand-in) + headless DrawBitmap driver with a row thread pool",
-            "port": "oracle port in the reference's configuration (atomic Halton counters + BVH + recursive integrator), g++ -O2"}
+    def drawbitmap_structure(self, n=2):
+        """Second, stated figure: the reference's own frame structure (serial GenerateRays :132-161, parallel trace :177-184,
+        parallel resolve :186-214)."""
+        if self.world is None:
+            return None
+        t0 = time.perf_counter()
+        st = self.frames(n, self.orc.FLAG_REF_DRAWBITMAP)
+        el = time.perf_counter() - t0
+        return {"value": st.paths / el, "unit": "path samples/s", "frames": n}
 
 
 def cpu_baseline(workload, budget_s):
     """Bounded sample: whole frames (1 spp over every pixel of the workload) until ~budget_s of CPU time."""
-    import numpy as np
-    orc, osc, cp, (w, h, depth) = oracle_setup(workload)
-    cores = os.cpu_count() or 1
-    hdr = np.zeros((h, w, 4), np.float32)
+    arm = CpuArm(workload)
+    arm.frames(1)                                            # first touch: page in, spin the pool up
     t0 = time.perf_counter()
     frames, paths = 0, 0
     while True:
-        st, kind = cpu_frame(orc, osc, cp, w, h, depth, frames + 1, hdr)
+        st = arm.frames(1)
         frames += 1
         paths += st.paths
         el = time.perf_counter() - t0
-        if el >= budget_s or el + el / frames > 2.5 * budget_s:
+        if el >= budget_s or el + el / frames > 1.5 * budget_s:
             break
-    return {"value": paths / el, "unit": "path samples/s", "cores": cores, "kind": kind,
-            "sample": f"{frames} full frame(s) (1 spp each, {w}x{h}, depth {depth}) of the workload in {el:.1f} s on {cores} threads; {CPU_NOTE[kind]}"}
+    out = {"value": paths / el, "unit": "path samples/s"}
+    out.update(arm.describe())
+    out["sample"] = (f"{frames} full frame(s) (1 spp each, {arm.w}x{arm.h}, depth {arm.depth}) of the workload in {el:.1f} s on {arm.threads} threads "
+                     f"after 1 untimed frame; scene from oracle/scenes/*.rtsc")
+    out["drawbitmap_structure"] = arm.drawbitmap_structure(2)
+    return out
 
 
 def run_reference(args):
@@ -119,30 +137,25 @@ def run_reference(args):
     if rank != 0:
         return 0
     scene_name, w, h, depth, cfg_spp, desc = WORKLOADS[args.workload]
-    import numpy as np
-    orc, osc, cp, _ = oracle_setup(args.workload)
-    cores = os.cpu_count() or 1
-    hdr = np.zeros((h, w, 4), np.float32)
-    frame = 0
-    kind = "port"
+    arm = CpuArm(args.workload)
     for _ in range(args.warmup):
-        frame += 1
-        cpu_frame(orc, osc, cp, w, h, depth, frame, hdr)
+        arm.frames(1)
     t0 = time.perf_counter()
     paths = 0
     for _ in range(args.steps):
-        frame += 1
-        st, kind = cpu_frame(orc, osc, cp, w, h, depth, frame, hdr)
-        paths += st.paths
+        paths += arm.frames(1).paths
     el = time.perf_counter() - t0
     value = paths / el
-    sample = f"each step = 1 full frame (1 spp, {w}x{h}, depth {depth}) on {cores} host threads; {CPU_NOTE[kind]}"
+    sample = f"each step = 1 full frame (1 spp, {w}x{h}, depth {depth}) on {arm.threads} host threads; frames continue one persistent world"
+    cb = {"value": value, "unit": "path samples/s", "sample": sample}
+    cb.update(arm.describe())
+    cb["drawbitmap_structure"] = arm.drawbitmap_structure(2)
     line = {"impl": "reference", "metric": "path samples/s", "value": value, "unit": "path samples/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * el / max(args.steps, 1), "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": f"{args.workload} {desc}", "scene": scene_name, "width": w, "height": h, "max_depth": depth,
-                       "spp_per_step": 1, "note": "the reference's Win32/Direct2D shell cannot build here; its common-lib sources can: " + CPU_NOTE[kind]},
-            "cpu_baseline": {"value": value, "unit": "path samples/s", "cores": cores, "kind": kind, "sample": sample},
+                       "spp_per_step": 1, "note": "the reference's Win32/Direct2D shell cannot build here; its common-lib sources can (oracle/_ref)"},
+            "cpu_baseline": cb,
             "e2e": {"value": value, "unit": "path samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     _emit(line)
     return 0
@@ -345,6 +358,8 @@ def run_b200(args):
         dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
     e2e_value = paths / float(e2e_s.item())
 
+    parity_n = parity_across_gpus(rt, ShardedRenderer, scene, depth, world, rank, local) if world > 1 else None
+
     if rank == 0:
         kern_s = float(kern_ms.item()) * 1e-3
         tests = float(counts[3].item())
@@ -369,6 +384,8 @@ def run_b200(args):
                          "sphere_tests_per_s": tests / kern_s / world, "kernel_ms_per_step": 1e3 * kern_s / args.steps},
             "clocks": clocks, "wall_s": t_wall,
         }
+        if parity_n is not None:
+            line["parity_n"] = parity_n
         if other is not None:
             other["speedup_vs_value"] = other["value"] / value
             line["accel"] = other
@@ -381,6 +398,54 @@ def run_b200(args):
         dist.barrier()
         dist.destroy_process_group()
     return 0
+
+
+def parity_across_gpus(rt, ShardedRenderer, scene, depth, world, rank, local, w=480, h=270, spp_per_gpu=8):
+    """N > 1 must equal N = 1 (one running sum per pixel, spheres-app.cpp:177-184): a small job of the same
+    scene rendered (a) sharded over the N ranks by sample range and sum-reduced onto rank 0, in TWO calls so that the
+    multi-call protocol (ranks >= 1 start each call from zero) is covered, and (b) on rank 0's GPU alone over the same frame
+    range.  Asserted: sample-count channel exactly equal, xyz within 1e-5 relative (the reduction order differs), and
+    rt_primary_hits buffers identical on every rank.  Runs after the timed region; returns the figures (rank 0)."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    cam = rt.scenes.default_camera(aspect=w / h)
+    spp = world * spp_per_gpu
+    out = {"width": w, "height": h, "spp": spp, "max_depth": depth, "calls": 2}
+    for name, flags in (("brute", 0), ("accel", rt.RT_FLAG_ACCEL)):
+        sr = ShardedRenderer(w, h, device=local)
+        sr.set_scene(scene)
+        sr.set_camera(cam)
+        sr.clear()
+        half = spp // 2 + 1                                   # uneven split: ranks get shares that differ by one frame
+        sr.render(half, depth, flags, first_sample=1, reduce=True)
+        sr.render(spp - half, depth, flags, first_sample=1 + half, reduce=True)
+        torch.cuda.synchronize()
+        ids, mids = sr.renderer.primary_hits(1, flags)        # jitter + lens off (the bit-exact sub-test of configs[1])
+        mine = torch.from_numpy(np.stack([ids, mids]).astype(np.int32)).to(f"cuda:{local}")
+        gathered = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(gathered, mine)
+        if rank == 0:
+            sharded = sr.hdr.cpu().numpy()
+            one = rt.Renderer(device=local, width=w, height=h)
+            one.set_scene(scene)
+            one.set_camera(cam)
+            one.render(spp, depth, flags, first_sample=1)
+            single = one.read_hdr_sum()
+            ids1, mids1 = one.primary_hits(1, flags)
+            one.close()
+            count_equal = bool(np.array_equal(sharded[..., 3], single[..., 3]) and np.all(single[..., 3] == spp))
+            a, b = sharded[..., :3].astype(np.float64), single[..., :3].astype(np.float64)
+            rel = float(np.max(np.abs(a - b) / np.maximum(np.abs(b), 1e-3 * b.mean())))
+            ref_ids = torch.from_numpy(np.stack([ids1, mids1]).astype(np.int32)).to(f"cuda:{local}")
+            hits_equal = all(bool(torch.equal(g, ref_ids)) for g in gathered)
+            out[name] = {"max_rel_diff_xyz": rel, "sample_count_equal": count_equal, "primary_hits_identical_on_all_ranks": hits_equal,
+                         "bitwise_equal_xyz": bool(np.array_equal(sharded[..., :3], single[..., :3]))}
+            assert count_equal, f"parity_n[{name}]: sample-count channel differs between {world} GPUs and 1 GPU"
+            assert rel < 1e-5, f"parity_n[{name}]: N={world} vs N=1 max relative difference {rel}"
+            assert hits_equal, f"parity_n[{name}]: primary-hit buffers differ across ranks"
+        dist.barrier()
+    return out if rank == 0 else None
 
 
 def _ncu_traffic(workload: str, query: str):

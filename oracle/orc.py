@@ -20,6 +20,7 @@ TEXTURE_DTYPE = np.dtype([("kind", "<i4"), ("tiling", "<f4"), ("c0", "<f4", (4,)
 LIGHT_DTYPE = np.dtype([("dir", "<f4", (3,)), ("color", "<f4", (4,)), ("luminance", "<f4")])
 
 FLAG_JITTER_OFF, FLAG_LENS_OFF = 1, 2
+FLAG_REF_DRAWBITMAP = 4      # tier A only: serial GenerateRays + parallel trace + parallel resolve (the reference's frame structure)
 RNG_COUNTER, RNG_HALTON = 0, 1
 ACCEL_BRUTE, ACCEL_BVH = 0, 1
 INTEGRATOR_ITERATIVE, INTEGRATOR_RECURSIVE = 0, 1
@@ -152,8 +153,53 @@ class Scene:
         return Scene(flat.spheres, flat.materials, flat.textures, flat.lights, flat.sky_luminance, flat.sky_texture)
 
 
+    @staticmethod
+    def from_rtsc(path: str) -> "Scene":
+        """Reads a flat scene file "RTSC" v1 (apps/spheres --dump-scene; byte layout of rt_scene_export) with numpy only --
+        the reference arm of bench.py takes its input from the committed oracle/scenes/*.rtsc and never maps the product library."""
+        b = open(path, "rb").read()
+        if len(b) < 32 or b[:4] != b"RTSC":
+            raise ValueError(f"{path}: not an RTSC scene file")
+        ver, ns, nm, nt, nl = np.frombuffer(b, "<i4", 5, 4)
+        if ver != 1 or min(ns, nm, nt, nl) < 0:
+            raise ValueError(f"{path}: unsupported RTSC version/counts")
+        sky_lum = float(np.frombuffer(b, "<f4", 1, 24)[0])
+        sky_tex = int(np.frombuffer(b, "<i4", 1, 28)[0])
+        p, out = 32, []
+        for dt, n in ((SPHERE_DTYPE, ns), (MATERIAL_DTYPE, nm), (TEXTURE_DTYPE, nt), (LIGHT_DTYPE, nl)):
+            if p + n * dt.itemsize > len(b):
+                raise ValueError(f"{path}: truncated RTSC file")
+            out.append(np.frombuffer(b, dt, n, p).copy())
+            p += n * dt.itemsize
+        return Scene(out[0], out[1], out[2], out[3], sky_lum, sky_tex)
+
+    def to_rtsc(self, path: str) -> None:
+        hdr = b"RTSC" + np.array([1, len(self.spheres), len(self.materials), len(self.textures), len(self.lights)], "<i4").tobytes()
+        hdr += np.array([self.c.sky_luminance], "<f4").tobytes() + np.array([self.c.sky_texture], "<i4").tobytes()
+        with open(path, "wb") as f:
+            f.write(hdr + self.spheres.tobytes() + self.materials.tobytes() + self.textures.tobytes() + self.lights.tobytes())
+
+
+SCENES_DIR = os.path.join(HERE, "scenes")
+
+
+def frozen_scene(name: str) -> Scene:
+    """oracle/scenes/<name>.rtsc: the bench / golden scenes frozen as files (oracle/scenes/freeze_scenes.py wrote them from
+    cpuraytracer_b200.scenes; tests/test_host_api.py checks they still agree byte for byte)."""
+    return Scene.from_rtsc(os.path.join(SCENES_DIR, name + ".rtsc"))
+
+
 def camera_params(origin, look_at, vfov_deg, aspect, focus, aperture) -> OrcCameraParams:
     return OrcCameraParams(f3(*origin), f3(*look_at), vfov_deg, aspect, focus, aperture)
+
+
+def default_camera_params(aspect: float, aperture: float = 0.4) -> OrcCameraParams:
+    """SpheresApp::InitCamera (spheres-app.cpp:35-49): origin (12, 2, -2.5), look-at (0, 1, 0), vfov 25 (spheres-app.h:10),
+    focus = |origin - lookAt| in float32 (XMVector3Length order), aperture 0.4 (spheres-app.h:11)."""
+    f = np.float32
+    d = np.array([12.0, 2.0, -2.5], f) - np.array([0.0, 1.0, 0.0], f)
+    focus = np.sqrt(f(f(d[0] * d[0] + d[1] * d[1]) + d[2] * d[2]))
+    return camera_params((12.0, 2.0, -2.5), (0.0, 1.0, 0.0), 25.0, float(f(aspect)), float(focus), aperture)
 
 
 def config(width, height, spp=1, max_depth=50, first_sample=1, flags=0, rng_mode=RNG_COUNTER, accel=ACCEL_BRUTE,
@@ -246,8 +292,52 @@ def load_ref():
     lib.ref_shade_hit.argtypes = [C.POINTER(OrcScene), FP, FP, FP, FP]
     lib.ref_build_info.restype = C.c_char_p
     lib.ref_build_info.argtypes = []
+    lib.ref_world_create.restype = P
+    lib.ref_world_create.argtypes = [C.POINTER(OrcScene), C.POINTER(OrcCameraParams), C.c_int]
+    lib.ref_world_destroy.restype = None
+    lib.ref_world_destroy.argtypes = [P]
+    lib.ref_world_threads.restype = C.c_int
+    lib.ref_world_threads.argtypes = [P]
+    lib.ref_world_render.restype = C.c_int
+    lib.ref_world_render.argtypes = [P, C.POINTER(OrcConfig), P, C.POINTER(OrcStats)]
     _ref = lib
     return lib
+
+
+class RefWorld:
+    """SpheresApp after InitScene / InitCamera on the reference's own classes: scene, BVH, per-material Halton counters and
+    the worker pool persist across render() calls, as they do between the reference's DrawBitmap calls."""
+
+    def __init__(self, scene: Scene, cam: OrcCameraParams, threads: int = 0, lib=None):
+        self.lib = lib if lib is not None else load_ref()
+        if self.lib is None:
+            raise RuntimeError("oracle/_ref/libref.so is not built (needs /root/reference)")
+        self._scene = scene
+        self.h = self.lib.ref_world_create(C.byref(scene.c), C.byref(cam), threads)
+        if not self.h:
+            raise ValueError("ref_world_create: bad argument")
+        self.threads = self.lib.ref_world_threads(self.h)
+
+    def render(self, cfg: OrcConfig, hdr: np.ndarray | None = None):
+        if hdr is None:
+            hdr = np.zeros((cfg.height, cfg.width, 4), np.float32)
+        assert hdr.dtype == np.float32 and hdr.flags.c_contiguous and hdr.size == 4 * cfg.width * cfg.height
+        st = OrcStats()
+        rc = self.lib.ref_world_render(self.h, C.byref(cfg), hdr.ctypes.data, C.byref(st))
+        if rc != 0:
+            raise ValueError(f"ref_world_render: bad argument ({rc})")
+        return hdr, st
+
+    def close(self):
+        if self.h:
+            self.lib.ref_world_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 def ref_render(scene: Scene, cam: OrcCameraParams, cfg: OrcConfig, hdr: np.ndarray | None = None):

@@ -9,7 +9,10 @@
 // requires the two to agree bit for bit when the oracle runs in ORC_MATH_REFERENCE mode.
 #include <atomic>
 #include <chrono>
+#include <condition_variable>
+#include <functional>
 #include <map>
+#include <mutex>
 #include <thread>
 
 #include "camera.h"
@@ -22,6 +25,69 @@
 #include "rt_oracle.h"
 
 namespace {
+
+// Ray counters are INSTRUMENTATION the reference does not have (spheres-app.cpp:224-236, :124-128).  They are plain
+// thread-local increments -- no shared cache line is touched per ray -- and every worker adds its totals to the world once
+// per job (per frame), so the timed region carries no contention the reference would not have.
+thread_local uint64_t tl_closest = 0, tl_shadow = 0;
+#ifdef REF_SHARED_ATOMIC_COUNTERS
+// Round-1 instrumentation (two adjacent std::atomic counters bumped by every ray of every thread), kept ONLY so that the
+// A/B in profiles/ (r02_cpu_baseline_ab.txt) can be re-measured: `make -C oracle ref_ab` builds _ref/libref_r01counters.so.
+std::atomic<uint64_t> g_closest_shared{0}, g_shadow_shared{0};
+#define REF_COUNT_CLOSEST() (g_closest_shared.fetch_add(1, std::memory_order_relaxed), ++tl_closest)
+#define REF_COUNT_SHADOW()  (g_shadow_shared.fetch_add(1, std::memory_order_relaxed), ++tl_shadow)
+#else
+#define REF_COUNT_CLOSEST() (++tl_closest)
+#define REF_COUNT_SHADOW()  (++tl_shadow)
+#endif
+
+// Persistent worker pool: the reference's std::for_each(std::execution::par, ...) (spheres-app.cpp:177-184) runs on the
+// runtime's pool, which outlives the frame; so does this one.  run(n, fn) executes fn(k) for k in [0, n), work handed out
+// by one atomic per item (items are rows or ray-buffer blocks: thousands of rays each), and returns when all are done.
+class Pool {
+public:
+    explicit Pool(int threads) : n_threads_(threads < 1 ? 1 : threads) {
+        for (int t = 1; t < n_threads_; ++t) workers_.emplace_back([this] { loop(); });
+    }
+    ~Pool() {
+        { std::lock_guard<std::mutex> g(m_); stop_ = true; ++generation_; }
+        cv_.notify_all();
+        for (auto& th : workers_) th.join();
+    }
+    int threads() const { return n_threads_; }
+    void run(int n, const std::function<void(int)>& fn, std::atomic<uint64_t>& closest, std::atomic<uint64_t>& shadow) {
+        {
+            std::lock_guard<std::mutex> g(m_);
+            fn_ = &fn; n_ = n; next_.store(0); pending_ = static_cast<int>(workers_.size()); closest_ = &closest; shadow_ = &shadow;
+            ++generation_;
+        }
+        cv_.notify_all();
+        tl_closest = tl_shadow = 0;                                         // the caller may have used the unit-level entry points before
+        work();                                                             // the calling thread is worker 0
+        std::unique_lock<std::mutex> g(m_);
+        done_.wait(g, [this] { return pending_ == 0; });
+    }
+private:
+    void work() {
+        for (int k; (k = next_.fetch_add(1, std::memory_order_relaxed)) < n_;) (*fn_)(k);
+        closest_->fetch_add(tl_closest, std::memory_order_relaxed); shadow_->fetch_add(tl_shadow, std::memory_order_relaxed);
+        tl_closest = tl_shadow = 0;
+    }
+    void loop() {
+        uint64_t seen = 0;
+        for (;;) {
+            { std::unique_lock<std::mutex> g(m_); cv_.wait(g, [&] { return generation_ != seen; }); seen = generation_; if (stop_) return; }
+            work();
+            { std::lock_guard<std::mutex> g(m_); if (--pending_ == 0) done_.notify_one(); }
+        }
+    }
+    int n_threads_;
+    std::vector<std::thread> workers_;
+    std::mutex m_; std::condition_variable cv_, done_;
+    uint64_t generation_ = 0; bool stop_ = false; int pending_ = 0;
+    const std::function<void(int)>* fn_ = nullptr; int n_ = 0; std::atomic<int> next_{0};
+    std::atomic<uint64_t>* closest_ = nullptr; std::atomic<uint64_t>* shadow_ = nullptr;
+};
 
 XMVECTOR v3(const float* p) { return XMVectorSet(p[0], p[1], p[2], 0.f); }
 void st3(float* p, FXMVECTOR v) { XMFLOAT3 f; XMStoreFloat3(&f, v); p[0] = f.x; p[1] = f.y; p[2] = f.z; }
@@ -38,8 +104,10 @@ struct RefWorld {
     std::map<const Material*, int> sphere_of;      // Payload carries the material pointer only
     std::vector<int> kind_of;                      // material kind per sphere index
     std::vector<Sphere*> spheres;                  // non-owning, insertion order (the BVH owns them afterwards)
-    std::atomic<uint64_t> closest{0}, shadow{0};
+    std::atomic<uint64_t> closest{0}, shadow{0};   // totals; written once per worker and job (see tl_closest above)
     int max_depth = 50;
+    std::unique_ptr<Pool> pool;
+    std::vector<std::pair<Ray, int>> ray_buffer;   // ORC_FLAG_REF_DRAWBITMAP: GenerateRays' buffer, spheres-app.cpp:132-161
 
     // InitScene (spheres-app.cpp:51-130) from a flat description instead of the unseeded generator.
     void build(const orc_scene* s, bool with_bvh) {
@@ -68,7 +136,7 @@ struct RefWorld {
         if (s->sky_texture >= 0) sky = std::make_unique<Emissive>(s->sky_luminance, textures[s->sky_texture].get());   // :120-121
         auto occlusion = [this](const Ray& ray) -> bool {                   // :124-128
             Payload dummy{};
-            shadow.fetch_add(1, std::memory_order_relaxed);
+            REF_COUNT_SHADOW();
             return bvh && bvh->Intersect(ray, dummy);
         };
         for (int i = 0; i < s->n_lights; ++i) {
@@ -82,7 +150,7 @@ struct RefWorld {
                                           p->vfov_deg, p->aspect, p->focus, p->aperture);
     }
     bool closest_hit(const Ray& ray, Payload& hit) {                        // GetClosestIntersection, :224-236
-        closest.fetch_add(1, std::memory_order_relaxed);
+        REF_COUNT_CLOSEST();
         return bvh && bvh->Intersect(ray, hit);
     }
     // GetHitColor, :238-257: emit + direct + (recurse ? attenuation * indirect : 0); sky on a miss.
@@ -110,53 +178,92 @@ struct RefWorld {
     }
 };
 
-template <class F> void parallel_rows(int height, int threads, F&& fn) {
-    if (threads <= 1) { for (int j = 0; j < height; ++j) fn(j); return; }
-    std::atomic<int> next{0};
-    std::vector<std::thread> pool;
-    for (int t = 0; t < threads; ++t) pool.emplace_back([&] { for (int j; (j = next.fetch_add(1)) < height;) fn(j); });
-    for (auto& th : pool) th.join();
-}
-int thread_count(const orc_config* cfg) {
-    const int t = cfg->threads > 0 ? cfg->threads : static_cast<int>(std::thread::hardware_concurrency());
+int thread_count(int requested) {
+    const int t = requested > 0 ? requested : static_cast<int>(std::thread::hardware_concurrency());
     return t < 1 ? 1 : t;
 }
 
 }  // namespace
 
+struct ref_world { RefWorld w; };
+
 extern "C" {
 
-// `spp` x DrawBitmap (spheres-app.cpp:163-184) on the reference's classes.  rng / accel / integrator fields of the config
-// are ignored: this build IS the reference configuration (atomic Halton counters, BVH, recursion).
-int ref_render(const orc_scene* sc, const orc_camera_params* cp, const orc_config* cfg, float* hdr, orc_stats* stats) {
-    if (!sc || !cp || !cfg || !hdr || cfg->width <= 0 || cfg->height <= 0 || cfg->spp < 0 || cfg->first_sample < 1 || sc->sky_texture < 0) return 1;
-    RefWorld w;
-    w.build(sc, true);
-    w.set_camera(cp);
+void ref_resolve_ldr(const float* hdr, int64_t n_pixels, uint64_t sample_count, uint32_t* bgra8);
+
+// A persistent world = SpheresApp after InitScene / InitCamera: scene, BVH, per-material Halton counters (material.h:34,
+// 50-51,67) and the worker pool live across frames, as they do in the reference between DrawBitmap calls.
+ref_world* ref_world_create(const orc_scene* sc, const orc_camera_params* cp, int threads) {
+    if (!sc || !cp || sc->sky_texture < 0) return nullptr;
+    ref_world* h = new ref_world();
+    h->w.build(sc, true);
+    h->w.set_camera(cp);
+    h->w.pool = std::make_unique<Pool>(thread_count(threads));
+    return h;
+}
+void ref_world_destroy(ref_world* h) { delete h; }
+int ref_world_threads(const ref_world* h) { return h && h->w.pool ? h->w.pool->threads() : 0; }
+
+// `spp` x DrawBitmap (spheres-app.cpp:163-184) on the reference's classes, continuing the world's sampler state.  rng /
+// accel / integrator fields of the config are ignored: this build IS the reference configuration (atomic Halton counters,
+// BVH, recursion).  Default schedule: rows handed to the pool, primary ray generated by the worker that traces it (the
+// kinder schedule for the CPU).  ORC_FLAG_REF_DRAWBITMAP: the reference's own frame structure -- GenerateRays fills the ray
+// buffer SERIALLY (:132-161), the trace runs in parallel over the buffer (:177-184), then the parallel resolve pass
+// (:186-214) -- i.e. what SpheresApp::OnRender times (:20-26) minus the Direct2D blit.
+int ref_world_render(ref_world* h, const orc_config* cfg, float* hdr, orc_stats* stats) {
+    if (!h || !cfg || !hdr || cfg->width <= 0 || cfg->height <= 0 || cfg->spp < 0 || cfg->first_sample < 1) return 1;
+    RefWorld& w = h->w;
     w.max_depth = cfg->max_depth;
-    const int threads = thread_count(cfg);
+    w.closest.store(0); w.shadow.store(0);
     const float exposure = std::pow(2, cfg->exposure_stops);                // :174
+    const int W = cfg->width, H = cfg->height;
+    std::vector<uint32_t> ldr;
     const auto t0 = std::chrono::steady_clock::now();
     for (int s = 0; s < cfg->spp; ++s) {
         const uint64_t n = cfg->first_sample + static_cast<uint64_t>(s);    // m_sampleCount after :168
         XMFLOAT2 jitter(0.f, 0.f);
         if (!(cfg->flags & ORC_FLAG_JITTER_OFF)) jitter = Random::HaltonSample2D(n, 2, 3);   // :140
-        parallel_rows(cfg->height, threads, [&](int j) {
-            for (int i = 0; i < cfg->width; ++i) {
-                const Ray ray = w.primary_ray(cfg, n, i, j, jitter);
-                const XMVECTOR c = w.hit_color(ray, 0) * exposure;          // :183
-                float* px = hdr + 4 * (static_cast<size_t>(j) * cfg->width + i);
-                XMFLOAT3 f; XMStoreFloat3(&f, c);
-                px[0] += f.x; px[1] += f.y; px[2] += f.z; px[3] += 1.0f;
-            }
-        });
+        auto accumulate = [&](const Ray& ray, size_t id) {
+            const XMVECTOR c = w.hit_color(ray, 0) * exposure;              // :183
+            float* px = hdr + 4 * id;
+            XMFLOAT3 f; XMStoreFloat3(&f, c);
+            px[0] += f.x; px[1] += f.y; px[2] += f.z; px[3] += 1.0f;
+        };
+        if (cfg->flags & ORC_FLAG_REF_DRAWBITMAP) {
+            w.ray_buffer.clear();
+            w.ray_buffer.reserve(static_cast<size_t>(W) * H);               // :135
+            int ray_id = 0;
+            for (int j = 0; j < H; ++j)
+                for (int i = 0; i < W; ++i) w.ray_buffer.push_back(std::make_pair(w.primary_ray(cfg, n, i, j, jitter), ray_id++));   // :144-158
+            const int block = 1024, n_blocks = (static_cast<int>(w.ray_buffer.size()) + block - 1) / block;
+            w.pool->run(n_blocks, [&](int k) {
+                const size_t e = std::min(w.ray_buffer.size(), static_cast<size_t>(k + 1) * block);
+                for (size_t r = static_cast<size_t>(k) * block; r < e; ++r) accumulate(w.ray_buffer[r].first, static_cast<size_t>(w.ray_buffer[r].second));
+            }, w.closest, w.shadow);
+            ldr.resize(static_cast<size_t>(W) * H);
+            w.pool->run(H, [&](int j) { ref_resolve_ldr(hdr + 4 * static_cast<size_t>(j) * W, W, n, ldr.data() + static_cast<size_t>(j) * W); }, w.closest, w.shadow);
+        } else {
+            w.pool->run(H, [&](int j) {
+                for (int i = 0; i < W; ++i) accumulate(w.primary_ray(cfg, n, i, j, jitter), static_cast<size_t>(j) * W + i);
+            }, w.closest, w.shadow);
+        }
     }
     if (stats) {
-        stats->paths = static_cast<uint64_t>(cfg->width) * cfg->height * cfg->spp;
+        stats->paths = static_cast<uint64_t>(W) * H * cfg->spp;
         stats->closest_rays = w.closest.load(); stats->shadow_rays = w.shadow.load();
         stats->seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     }
     return 0;
+}
+
+// One-shot form: a fresh world (sampler indices at 0) for this call only.
+int ref_render(const orc_scene* sc, const orc_camera_params* cp, const orc_config* cfg, float* hdr, orc_stats* stats) {
+    if (!sc || !cp || !cfg || !hdr || cfg->width <= 0 || cfg->height <= 0 || cfg->spp < 0 || cfg->first_sample < 1 || sc->sky_texture < 0) return 1;
+    ref_world* h = ref_world_create(sc, cp, cfg->threads);
+    if (!h) return 1;
+    const int rc = ref_world_render(h, cfg, hdr, stats);
+    ref_world_destroy(h);
+    return rc;
 }
 
 int ref_primary_hits(const orc_scene* sc, const orc_camera_params* cp, const orc_config* cfg, int32_t* sphere_idx, int32_t* material_id) {
@@ -167,7 +274,8 @@ int ref_primary_hits(const orc_scene* sc, const orc_camera_params* cp, const orc
     const uint64_t n = cfg->first_sample;
     XMFLOAT2 jitter(0.f, 0.f);
     if (!(cfg->flags & ORC_FLAG_JITTER_OFF)) jitter = Random::HaltonSample2D(n, 2, 3);
-    parallel_rows(cfg->height, thread_count(cfg), [&](int j) {
+    Pool pool(thread_count(cfg->threads));
+    pool.run(cfg->height, [&](int j) {
         for (int i = 0; i < cfg->width; ++i) {
             Payload hit{};
             const bool ok = w.closest_hit(w.primary_ray(cfg, n, i, j, jitter), hit);
@@ -176,7 +284,7 @@ int ref_primary_hits(const orc_scene* sc, const orc_camera_params* cp, const orc
             if (sphere_idx) sphere_idx[id] = idx;
             if (material_id) material_id[id] = ok ? w.kind_of[idx] : ORC_MAT_SKY;
         }
-    });
+    }, w.closest, w.shadow);
     return 0;
 }
 
@@ -259,7 +367,13 @@ int ref_shade_hit(const orc_scene* sc, const float view_origin[3], const float o
     return w.sphere_of.at(hit.material);
 }
 const char* ref_build_info(void) {
-    return "tier-A: reference camera/light/material/quasi-random/ray-tracing/texture .cpp compiled unmodified against oracle/dxm_shim; compiler " __VERSION__;
+    return "tier-A: reference camera/light/material/quasi-random/ray-tracing/texture .cpp compiled unmodified against oracle/dxm_shim; g++ " __VERSION__
+           " -O2 (x86-64 SSE2 baseline, -ffp-contract=off); ray counters: "
+#ifdef REF_SHARED_ATOMIC_COUNTERS
+           "shared atomics (round-1 instrumentation, A/B build)";
+#else
+           "per-thread";
+#endif
 }
 
 }  // extern "C"

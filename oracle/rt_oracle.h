@@ -48,7 +48,8 @@ typedef struct orc_camera_params {
 } orc_camera_params;
 typedef struct orc_camera { float origin[3], x[3], y[3], image_origin[3]; float aperture, focus; } orc_camera;
 
-enum { ORC_FLAG_JITTER_OFF = 1u, ORC_FLAG_LENS_OFF = 2u };
+enum { ORC_FLAG_JITTER_OFF = 1u, ORC_FLAG_LENS_OFF = 2u,
+       ORC_FLAG_REF_DRAWBITMAP = 4u };  /* tier A (ref_driver.cpp) only: the reference's frame structure -- serial GenerateRays, parallel trace, parallel resolve */
 enum { ORC_RNG_COUNTER = 0, ORC_RNG_HALTON = 1 };     /* HALTON = the reference's per-material atomic counters */
 enum { ORC_ACCEL_BRUTE = 0, ORC_ACCEL_BVH = 1 };      /* BVH = the reference's BvhNode restated */
 enum { ORC_INTEGRATOR_ITERATIVE = 0, ORC_INTEGRATOR_RECURSIVE = 1 };
