@@ -4,7 +4,7 @@
 The compute path is csrc/librt_b200.so (hand-written CUDA, C ABI in include/rt_b200.h); this package
 is the thin host-side mirror of the reference interface.  There is no CPU fallback.
 """
-from ._lib import (LIB_PATH, RT_FLAG_DEBUG_NO_CULL, RT_FLAG_JITTER_OFF, RT_FLAG_LENS_OFF, RT_FLAG_WAVEFRONT, RT_FLAG_ACCEL, RT_FLAG_HALTON, RT_MAT_METAL, RT_MAT_OPAQUE,
+from ._lib import (LIB_PATH, RT_FLAG_DEBUG_NO_CULL, RT_FLAG_JITTER_OFF, RT_FLAG_LENS_OFF, RT_FLAG_WAVEFRONT, RT_FLAG_ACCEL, RT_FLAG_HALTON, RT_FLAG_OVERWRITE, RT_FLAG_DEBUG_ONE_KERNEL, RT_MAT_METAL, RT_MAT_OPAQUE,
                    RT_MAT_SKY, RT_MAT_TRANSPARENT, RtError, load)
 from .api import (Camera, CheckerTexture, ConstTexture, DielectricOpaque, DielectricTransparent, DirectionalLight,
                   Emissive, FlatScene, Metal, Renderer, Scene, Sphere, XMCOLOR)

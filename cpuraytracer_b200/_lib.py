@@ -20,6 +20,7 @@ STATUS_NAMES = {0: "RT_OK", 1: "RT_ERR_INVALID_ARGUMENT", 2: "RT_ERR_CUDA", 3: "
 RT_MAT_OPAQUE, RT_MAT_METAL, RT_MAT_TRANSPARENT, RT_MAT_SKY = 0, 1, 2, 3
 RT_TEX_CONST, RT_TEX_CHECKER = 0, 1
 RT_FLAG_JITTER_OFF, RT_FLAG_LENS_OFF, RT_FLAG_WAVEFRONT, RT_FLAG_ACCEL, RT_FLAG_HALTON, RT_FLAG_DEBUG_NO_CULL = 1, 2, 4, 8, 16, 0x100
+RT_FLAG_OVERWRITE, RT_FLAG_DEBUG_ONE_KERNEL = 32, 0x200
 
 # flat scene description v1 (byte-identical to the structs in include/rt_b200.h)
 SPHERE_DTYPE = np.dtype([("cx", "<f4"), ("cy", "<f4"), ("cz", "<f4"), ("radius", "<f4"), ("material", "<i4")])
@@ -91,6 +92,7 @@ SYMBOLS = [
     ("rt_set_seed", C.c_int, [_P, C.c_uint32]),
     ("rt_sampler_reset", C.c_int, [_P]),
     ("rt_set_chunk_spp", C.c_int, [_P, C.c_int]),
+    ("rt_set_accel_group_slots", C.c_int, [_P, C.c_int]),
     ("rt_framebuffer_resize", C.c_int, [_P, C.c_int, C.c_int]),
     ("rt_framebuffer_clear", C.c_int, [_P]),
     ("rt_render", C.c_int, [_P, C.c_uint64, C.c_int, C.c_int, C.c_uint32]),
@@ -101,6 +103,7 @@ SYMBOLS = [
     ("rt_hdr_device_ptr", _P, [_P]),
     ("rt_hdr_bind_external", C.c_int, [_P, _P]),
     ("rt_scene_accel_image", C.c_int, [_P, _P, C.c_size_t, C.POINTER(AccelImageInfo)]),
+    ("rt_scene_accel_image_slots", C.c_int, [_P, C.c_int, _P, C.c_size_t, C.POINTER(AccelImageInfo)]),
     ("rt_get_stats", C.c_int, [_P, C.POINTER(Stats)]),
     ("rt_stats_reset", C.c_int, [_P]),
     ("rt_build_info", C.c_char_p, []),

@@ -139,13 +139,14 @@ class Scene:
     def handle(self):
         return self._h
 
-    def accel_image(self):
-        """(info, image bytes) of the box hierarchy RT_FLAG_ACCEL stages for this scene (rt_scene_accel_image: host only, no
-        device needed); layout in include/rt_b200.h.  Raises RtError(RT_ERR_UNSUPPORTED) when the scene has no hierarchy."""
+    def accel_image(self, min_group_slots: int = 0):
+        """(info, image bytes) of the box hierarchy RT_FLAG_ACCEL stages for this scene (rt_scene_accel_image_slots: host only,
+        no device needed); layout in include/rt_b200.h.  min_group_slots: finest group size to try (8, 16, 32; 0 = default).
+        Raises RtError(RT_ERR_UNSUPPORTED) when the scene has no hierarchy."""
         info = L.AccelImageInfo()
-        L.check(self._lib.rt_scene_accel_image(self._h, None, 0, C.byref(info)))
+        L.check(self._lib.rt_scene_accel_image_slots(self._h, min_group_slots, None, 0, C.byref(info)))
         buf = np.zeros(info.bytes, dtype=np.uint8)
-        L.check(self._lib.rt_scene_accel_image(self._h, buf.ctypes.data_as(C.c_void_p), buf.nbytes, C.byref(info)))
+        L.check(self._lib.rt_scene_accel_image_slots(self._h, min_group_slots, buf.ctypes.data_as(C.c_void_p), buf.nbytes, C.byref(info)))
         return info, buf
 
     # -- low-level recorder (ids) --
@@ -290,6 +291,10 @@ class Renderer:
 
     def set_chunk_spp(self, chunk: int) -> None:
         L.check(self._lib.rt_set_chunk_spp(self._h, chunk))
+
+    def set_accel_group_slots(self, slots: int) -> None:
+        """RT_FLAG_ACCEL tuning: finest group size (8, 16 or 32 slots; 0 = default) the next set_scene may choose."""
+        L.check(self._lib.rt_set_accel_group_slots(self._h, slots))
 
     def render(self, spp: int, max_depth: int = 50, flags: int = 0, first_sample: Optional[int] = None) -> None:
         """`spp` x DrawBitmap.  first_sample defaults to continuing after the samples already accumulated."""

@@ -125,6 +125,7 @@ int rt_scene_add_texture_const(rt_scene* s, const float rgba[4]) {
 }
 int rt_scene_add_texture_checker(rt_scene* s, const float rgba0[4], const float rgba1[4], float tiling) {
     if (!s || !rgba0 || !rgba1) return -fail(RT_ERR_INVALID_ARGUMENT, "rt_scene_add_texture_checker: NULL argument");
+    if (!std::isfinite(tiling)) return -fail(RT_ERR_INVALID_ARGUMENT, "rt_scene_add_texture_checker: tiling must be finite");
     rt_texture_desc t{}; t.kind = RT_TEX_CHECKER; t.tiling = tiling;
     for (int k = 0; k < 4; ++k) { t.c0[k] = host::xmcolor_roundtrip(rgba0[k]); t.c1[k] = host::xmcolor_roundtrip(rgba1[k]); }
     s->textures.push_back(t);
@@ -132,6 +133,7 @@ int rt_scene_add_texture_checker(rt_scene* s, const float rgba0[4], const float 
 }
 static int add_material(rt_scene* s, int kind, int texture, float smoothness, float ior, const char* who) {
     if (!s) return -fail(RT_ERR_INVALID_ARGUMENT, "%s: scene is NULL", who);
+    if (!std::isfinite(smoothness)) return -fail(RT_ERR_INVALID_ARGUMENT, "%s: smoothness must be finite", who);
     if (kind != RT_MAT_TRANSPARENT && (texture < 0 || texture >= static_cast<int>(s->textures.size())))
         return -fail(RT_ERR_INVALID_ARGUMENT, "%s: texture id %d out of range [0,%zu)", who, texture, s->textures.size());
     rt_material_desc m{}; m.kind = kind; m.texture = kind == RT_MAT_TRANSPARENT ? -1 : texture; m.smoothness = smoothness; m.ior = ior;
@@ -141,7 +143,7 @@ static int add_material(rt_scene* s, int kind, int texture, float smoothness, fl
 int rt_scene_add_material_opaque(rt_scene* s, int texture, float smoothness) { return add_material(s, RT_MAT_OPAQUE, texture, smoothness, 0.f, "rt_scene_add_material_opaque"); }
 int rt_scene_add_material_metal(rt_scene* s, int texture, float smoothness) { return add_material(s, RT_MAT_METAL, texture, smoothness, 0.f, "rt_scene_add_material_metal"); }
 int rt_scene_add_material_transparent(rt_scene* s, float smoothness, float ior) {
-    if (!(ior > 0.f)) return -fail(RT_ERR_INVALID_ARGUMENT, "rt_scene_add_material_transparent: ior must be > 0");
+    if (!(ior > 0.f) || !std::isfinite(ior)) return -fail(RT_ERR_INVALID_ARGUMENT, "rt_scene_add_material_transparent: ior must be finite and > 0");
     return add_material(s, RT_MAT_TRANSPARENT, -1, smoothness, ior, "rt_scene_add_material_transparent");
 }
 int rt_scene_add_sphere(rt_scene* s, const float center[3], float radius, int material) {
@@ -191,13 +193,30 @@ int rt_scene_import(rt_scene* s, int32_t ns, const rt_sphere_desc* sp, int32_t n
                     int32_t nl, const rt_light_desc* li, float sky_lum, int32_t sky_tex) {
     if (!s || ns < 0 || nm < 0 || nt < 0 || nl < 0 || (ns && !sp) || (nm && !ma) || (nt && !te) || (nl && !li))
         return fail(RT_ERR_INVALID_ARGUMENT, "rt_scene_import: bad argument");
+    // the same checks the rt_scene_add_* recorders make, so that a scene file cannot carry what the recorder would refuse
+    for (int i = 0; i < nt; ++i) {
+        if (te[i].kind != RT_TEX_CONST && te[i].kind != RT_TEX_CHECKER) return fail(RT_ERR_INVALID_ARGUMENT, "rt_scene_import: texture %d has kind %d", i, te[i].kind);
+        bool ok = std::isfinite(te[i].tiling);
+        for (int k = 0; k < 4; ++k) ok = ok && std::isfinite(te[i].c0[k]) && std::isfinite(te[i].c1[k]);
+        if (!ok) return fail(RT_ERR_INVALID_ARGUMENT, "rt_scene_import: texture %d has a non-finite colour or tiling", i);
+    }
     for (int i = 0; i < nm; ++i) {
         if (ma[i].kind < RT_MAT_OPAQUE || ma[i].kind > RT_MAT_TRANSPARENT) return fail(RT_ERR_INVALID_ARGUMENT, "rt_scene_import: material %d has kind %d", i, ma[i].kind);
         if (ma[i].kind != RT_MAT_TRANSPARENT && (ma[i].texture < 0 || ma[i].texture >= nt)) return fail(RT_ERR_INVALID_ARGUMENT, "rt_scene_import: material %d texture out of range", i);
+        if (!std::isfinite(ma[i].smoothness)) return fail(RT_ERR_INVALID_ARGUMENT, "rt_scene_import: material %d has a non-finite smoothness", i);
+        if (ma[i].kind == RT_MAT_TRANSPARENT && !(ma[i].ior > 0.f && std::isfinite(ma[i].ior))) return fail(RT_ERR_INVALID_ARGUMENT, "rt_scene_import: material %d: ior must be finite and > 0", i);
     }
-    for (int i = 0; i < ns; ++i)
-        if (sp[i].material < 0 || sp[i].material >= nm || !(sp[i].radius > 0.f)) return fail(RT_ERR_INVALID_ARGUMENT, "rt_scene_import: sphere %d invalid", i);
-    if (sky_tex < 0 || sky_tex >= nt) return fail(RT_ERR_INVALID_ARGUMENT, "rt_scene_import: sky texture out of range");
+    for (int i = 0; i < ns; ++i) {
+        const float ctr[3] = {sp[i].cx, sp[i].cy, sp[i].cz};
+        if (sp[i].material < 0 || sp[i].material >= nm || !(sp[i].radius > 0.f) || !std::isfinite(sp[i].radius) || !finite3(ctr))
+            return fail(RT_ERR_INVALID_ARGUMENT, "rt_scene_import: sphere %d invalid (material id, finite centre, finite radius > 0)", i);
+    }
+    for (int i = 0; i < nl; ++i) {
+        const host::V3 nrm = host::normalize3({li[i].dir[0], li[i].dir[1], li[i].dir[2]});
+        if (!finite3(li[i].dir) || !(host::dot3(nrm, nrm) > 0.f) || !std::isfinite(li[i].luminance) || !finite3(li[i].color))
+            return fail(RT_ERR_INVALID_ARGUMENT, "rt_scene_import: light %d invalid (finite non-zero direction, finite colour and luminance)", i);
+    }
+    if (sky_tex < 0 || sky_tex >= nt || !std::isfinite(sky_lum)) return fail(RT_ERR_INVALID_ARGUMENT, "rt_scene_import: sky texture out of range or non-finite luminance");
     s->spheres.assign(sp, sp + ns); s->materials.assign(ma, ma + nm); s->textures.assign(te, te + nt); s->lights.assign(li, li + nl);
     s->sky_luminance = sky_lum; s->sky_texture = sky_tex;
     return RT_OK;
@@ -234,6 +253,9 @@ struct rt_context {
     uint32_t* ldr = nullptr;
     int32_t *ids = nullptr, *mids = nullptr;
     float4* partial = nullptr; size_t partial_bytes = 0;
+    uint16_t* hits = nullptr; size_t hits_bytes = 0;   // first-hit records of one batch (two-stage schedule)
+    int path_tpb = 0, path_bps = 0;                    // CTA size / resident CTAs per SM of the stage-2 kernel
+    int accel_gshift_min = 3;                          // finest group size rt_set_scene tries (rt_set_accel_group_slots)
     float2 *jitter = nullptr, *lens = nullptr; size_t jitter_cap = 0, lens_cap = 0;
     u64* counters = nullptr;   // [0] work counter, [1..4] stats
     // settings
@@ -247,7 +269,7 @@ struct rt_context {
     uint4* accel_blob = nullptr; bool accel_ok = false; std::string accel_why;
     struct ExtraLight { float L[3], lc[3], iL[3]; float2* cullC; };
     std::vector<ExtraLight> extra_lights; float2* extra_cullC = nullptr;   // lights 1.. (one additional launch each, see rt_render)
-    u64* sampler = nullptr; size_t n_sampler = 0;   // RT_FLAG_HALTON: per-material-instance Halton indices (material.h:34,50-51,67)
+    u64* sampler = nullptr; size_t n_sampler = 0;   // RT_FLAG_HALTON: per-material-instance Halton indices (material.h:34,50-51,67); second half = snapshot
     int accel_tpb = 0, accel_bps = 0;
 
     float4* hdr() const { return hdr_ext ? hdr_ext : hdr_own; }
@@ -257,7 +279,18 @@ static int ctx_use(rt_context* c) {
     RT_CUDA(cudaSetDevice(c->device));
     return RT_OK;
 }
+static void ev_account(rt_context* c, const EventPair& e) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, e.a, e.b) == cudaSuccess) { if (e.kind == 0) c->render_ms += ms; else c->resolve_ms += ms; }
+}
 static EventPair ev_begin(rt_context* c, int kind) {
+    // pairs whose end event has completed go back to the pool (their time is accounted now), so a long interactive loop
+    // that never asks for statistics keeps a bounded number of live CUDA events
+    size_t k = 0;
+    while (k < c->pending.size() && cudaEventQuery(c->pending[k].b) == cudaSuccess) ++k;     // one stream: completion is in order
+    if (k == 0 && c->pending.size() >= 256) { cudaEventSynchronize(c->pending[0].b); k = 1; }
+    for (size_t i = 0; i < k; ++i) { ev_account(c, c->pending[i]); c->pool.push_back(c->pending[i]); }
+    c->pending.erase(c->pending.begin(), c->pending.begin() + static_cast<std::ptrdiff_t>(k));
     EventPair e;
     if (!c->pool.empty()) { e = c->pool.back(); c->pool.pop_back(); }
     else { cudaEventCreate(&e.a); cudaEventCreate(&e.b); }
@@ -267,11 +300,7 @@ static EventPair ev_begin(rt_context* c, int kind) {
 }
 static void ev_end(rt_context* c, EventPair e) { cudaEventRecord(e.b, c->stream); c->pending.push_back(e); }
 static void ev_collect(rt_context* c) {
-    for (auto& e : c->pending) {
-        float ms = 0.f;
-        if (cudaEventElapsedTime(&ms, e.a, e.b) == cudaSuccess) { if (e.kind == 0) c->render_ms += ms; else c->resolve_ms += ms; }
-        c->pool.push_back(e);
-    }
+    for (auto& e : c->pending) { ev_account(c, e); c->pool.push_back(e); }
     c->pending.clear();
 }
 template <class T> static int dev_realloc(T*& p, size_t n) {
@@ -312,12 +341,36 @@ template <int G> static const void* accel_primary_fn() { return reinterpret_cast
 static const void* accel_render_kernel(int gshift) { return gshift == 3 ? accel_render_fn<3>() : gshift == 4 ? accel_render_fn<4>() : accel_render_fn<5>(); }
 static const void* accel_primary_kernel(int gshift) { return gshift == 3 ? accel_primary_fn<3>() : gshift == 4 ? accel_primary_fn<4>() : accel_primary_fn<5>(); }
 
+// Two-stage schedule: kernel of a stage for (query mode, sampler, group size, direct-only).
+#define RT_FN(...) reinterpret_cast<const void*>(&__VA_ARGS__)
+template <int G> static const void* accel_path_fn(bool halton, bool direct) {
+    if (halton) return RT_FN(rt::rt_path_kernel<rt::MODE_ACCEL, true, G, false>);
+    return direct ? RT_FN(rt::rt_path_kernel<rt::MODE_ACCEL, false, G, true>) : RT_FN(rt::rt_path_kernel<rt::MODE_ACCEL, false, G, false>);
+}
+static const void* path_kernel(int mode, bool halton, int gshift, bool direct) {
+    if (mode == rt::MODE_ACCEL) return gshift == 3 ? accel_path_fn<3>(halton, direct) : gshift == 4 ? accel_path_fn<4>(halton, direct) : accel_path_fn<5>(halton, direct);
+    if (mode == rt::MODE_NO_CULL) return RT_FN(rt::rt_path_kernel<rt::MODE_NO_CULL, false, 5, false>);
+    if (halton) return RT_FN(rt::rt_path_kernel<rt::MODE_CULL, true, 5, false>);
+    return direct ? RT_FN(rt::rt_path_kernel<rt::MODE_CULL, false, 5, true>) : RT_FN(rt::rt_path_kernel<rt::MODE_CULL, false, 5, false>);
+}
+static const void* first_hit_kernel(int mode, int gshift) {
+    if (mode == rt::MODE_ACCEL) return gshift == 3 ? RT_FN(rt::rt_first_hit_kernel<rt::MODE_ACCEL, 3>) : gshift == 4 ? RT_FN(rt::rt_first_hit_kernel<rt::MODE_ACCEL, 4>) : RT_FN(rt::rt_first_hit_kernel<rt::MODE_ACCEL, 5>);
+    return mode == rt::MODE_NO_CULL ? RT_FN(rt::rt_first_hit_kernel<rt::MODE_NO_CULL, 5>) : RT_FN(rt::rt_first_hit_kernel<rt::MODE_CULL, 5>);
+}
+// Opt every kernel of a mode in to the large dynamic shared memory carve-out.
+static int optin_smem(int mode, int gshift, int optin) {
+    for (int h = 0; h < 2; ++h) for (int dd = 0; dd < 2; ++dd)
+        RT_CUDA(cudaFuncSetAttribute(path_kernel(mode, h != 0, gshift, dd != 0), cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
+    RT_CUDA(cudaFuncSetAttribute(first_hit_kernel(mode, gshift), cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
+    return RT_OK;
+}
+
 // Host half of build_accel: the position-independent image and its section table (no CUDA call, no context), also reachable
 // through rt_scene_accel_image() so that the CPU tests can check its invariants.  false + `why` = hierarchy unavailable.
-static bool make_accel_image(const rt_scene* s, rt::AccelParams& a, std::vector<unsigned char>& img, std::string& why) {
+static bool make_accel_image(const rt_scene* s, rt::AccelParams& a, std::vector<unsigned char>& img, std::string& why, int gshift_min = 3) {
     a = rt::AccelParams{};
     const int n = static_cast<int>(s->spheres.size());
-    if (n > 65000) { why = "more than 65000 spheres (slot -> index map is 16 bit)"; return false; }
+    if (n > 65000) { why = "more than 65000 spheres (slot -> index map and first-hit records are 16 bit)"; return false; }
     // big spheres: radius > 4 x median (at most 64, the largest first)
     std::vector<float> radii(n);
     for (int i = 0; i < n; ++i) radii[i] = s->spheres[i].radius;
@@ -343,10 +396,9 @@ static bool make_accel_image(const rt_scene* s, rt::AccelParams& a, std::vector<
     std::stable_sort(keyed.begin(), keyed.end(), [](const std::pair<uint32_t, int>& x, const std::pair<uint32_t, int>& y) { return x.first < y.first; });
     const int n_big_groups = (static_cast<int>(big.size()) + 31) / 32;
     // Slots per small group: the finest of 8 / 16 / 32 whose group count still fits the 32 x 8 fan-out of the two box levels
-    // (a ray then culls fewer spheres per touched box; measured in profiles/r01x_accel_group_size.txt).  RT_ACCEL_GSHIFT
-    // (3, 4 or 5) sets the finest size tried, for experiments.
-    int gshift = 3;
-    if (const char* e = std::getenv("RT_ACCEL_GSHIFT")) { const int v = std::atoi(e); if (v >= 3 && v <= 5) gshift = v; }
+    // (a ray then culls fewer spheres per touched box; measured in profiles/r01x_accel_group_size.txt).  gshift_min
+    // (rt_set_accel_group_slots: 8, 16 or 32 slots) sets the finest size tried.
+    int gshift = std::min(5, std::max(3, gshift_min));
     while (gshift < 5 && (static_cast<int>(small.size()) + (1 << gshift) - 1) / (1 << gshift) > RT_ACCEL_GSHIFT_MAX_GROUPS) ++gshift;
     const int GS = 1 << gshift;
     const int n_groups = (static_cast<int>(small.size()) + GS - 1) / GS;
@@ -447,7 +499,8 @@ static int build_accel(rt_context* c, const rt_scene* s) {
     c->accel_ok = false; c->accel_why.clear();
     rt::AccelParams& a = c->base.accel;
     std::vector<unsigned char> img;
-    if (!make_accel_image(s, a, img, c->accel_why)) return RT_OK;
+    if (!make_accel_image(s, a, img, c->accel_why, c->accel_gshift_min)) return RT_OK;
+    if (a.n_pairs * 2 > 65534) { c->accel_why = "more than 65534 slots in the hierarchy image (first-hit records are 16 bit)"; return RT_OK; }
     const size_t total = img.size();
     const int gshift = a.gshift;
     if (int r = dev_realloc(c->accel_blob, total / 16)) return r;
@@ -458,12 +511,15 @@ static int build_accel(rt_context* c, const rt_scene* s) {
     const int optin = static_cast<int>(c->prop.sharedMemPerBlockOptin);
     RT_CUDA(cudaFuncSetAttribute(accel_render_kernel(gshift), cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
     RT_CUDA(cudaFuncSetAttribute(accel_primary_kernel(gshift), cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
+    if (int r = optin_smem(rt::MODE_ACCEL, gshift, optin)) return r;
     int best_tpb = 0, best_bps = 0;
     for (int tpb = 128; tpb <= RT_ACCEL_MAX_TPB; tpb += 128) {
         const size_t smem = accel_cta_smem_bytes(a, tpb);
         if (smem > static_cast<size_t>(optin)) break;
-        int bps = 0;
-        RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, accel_render_kernel(gshift), tpb, smem));
+        int bps = 0, bps1 = 0;                               // the CTA shape must fit the one-kernel and the two-stage kernels alike
+        RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, path_kernel(rt::MODE_ACCEL, false, gshift, false), tpb, smem));
+        RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps1, accel_render_kernel(gshift), tpb, smem));
+        bps = std::min(bps, bps1);
         if (bps * tpb > best_bps * best_tpb) { best_tpb = tpb; best_bps = bps; }
     }
     if (best_bps < 1) { c->accel_why = "the hierarchy image does not fit in shared memory"; return RT_OK; }
@@ -505,7 +561,7 @@ void rt_context_destroy(rt_context* c) {
     for (auto& e : c->pool) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
     cudaFree(c->geom); cudaFree(c->wf_block); cudaFree(c->wf_live); cudaFree(c->accel_blob); cudaFree(c->sampler); cudaFree(c->extra_cullC);
     cudaFree(c->cullA); cudaFree(c->cullB); cudaFree(c->cullC); cudaFree(c->radius); cudaFree(c->mats);
-    cudaFree(c->hdr_own); cudaFree(c->ldr); cudaFree(c->ids); cudaFree(c->mids); cudaFree(c->partial);
+    cudaFree(c->hdr_own); cudaFree(c->ldr); cudaFree(c->ids); cudaFree(c->mids); cudaFree(c->partial); cudaFree(c->hits);
     cudaFree(c->jitter); cudaFree(c->lens); cudaFree(c->counters);
     if (c->own_stream) cudaStreamDestroy(c->stream);
     delete c;
@@ -532,6 +588,12 @@ int rt_sampler_reset(rt_context* c) {
     if (!c->sampler) return fail(RT_ERR_NOT_READY, "rt_sampler_reset: no scene set");
     if (int r = ctx_use(c)) return r;
     RT_CUDA(cudaMemsetAsync(c->sampler, 0, c->n_sampler * sizeof(u64), c->stream));
+    return RT_OK;
+}
+static int gshift_of_slots(int slots) { return slots == 0 || slots == 8 ? 3 : slots == 16 ? 4 : slots == 32 ? 5 : -1; }
+int rt_set_accel_group_slots(rt_context* c, int slots) {
+    if (!c || gshift_of_slots(slots) < 0) return fail(RT_ERR_INVALID_ARGUMENT, "rt_set_accel_group_slots: slots must be 0 (default), 8, 16 or 32");
+    c->accel_gshift_min = gshift_of_slots(slots);
     return RT_OK;
 }
 int rt_set_chunk_spp(rt_context* c, int chunk) {
@@ -589,8 +651,8 @@ int rt_set_scene(rt_context* c, const rt_scene* s) {
     if (int r = dev_realloc(c->radius, n_pad)) return r;
     if (int r = dev_realloc(c->mats, M.size())) return r;
     c->n_sampler = 2 * std::max<size_t>(1, s->materials.size());
-    if (int r = dev_realloc(c->sampler, c->n_sampler)) return r;
-    RT_CUDA(cudaMemsetAsync(c->sampler, 0, c->n_sampler * sizeof(u64), c->stream));      // the reference's indices start at 0 with the scene
+    if (int r = dev_realloc(c->sampler, 2 * c->n_sampler)) return r;    // [indices][snapshot taken before light 0's pass of a batch]
+    RT_CUDA(cudaMemsetAsync(c->sampler, 0, 2 * c->n_sampler * sizeof(u64), c->stream));      // the reference's indices start at 0 with the scene
     std::vector<float4> G(std::max(n, 1), make_float4(0.f, 0.f, 0.f, 1.f));
     for (int i = 0; i < n; ++i) G[i] = make_float4(s->spheres[i].cx, s->spheres[i].cy, s->spheres[i].cz, s->spheres[i].radius);
     if (int r = dev_realloc(c->geom, G.size())) return r;
@@ -651,14 +713,20 @@ int rt_set_scene(rt_context* c, const rt_scene* s) {
     RT_CUDA(cudaFuncSetAttribute(rt::rt_primary_kernel<rt::MODE_NO_CULL>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
     RT_CUDA(cudaFuncSetAttribute(rt::wf_intersect_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
     RT_CUDA(cudaFuncSetAttribute(rt::wf_intersect_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
+    if (int r = optin_smem(rt::MODE_CULL, 5, optin)) return r;
+    if (int r = optin_smem(rt::MODE_NO_CULL, 5, optin)) return r;
     int best_tpb = 0, best_bps = 0;
+    c->path_tpb = 0; c->path_bps = 0;
     for (int tpb = 128; tpb <= RT_MAX_TPB; tpb += 128) {
         const size_t smem = cta_smem_bytes(n_pad, tpb);
         if (smem > static_cast<size_t>(optin)) break;
         int bps = 0;
         RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, rt::rt_render_kernel<rt::MODE_CULL>, tpb, smem));
         if (bps * tpb > best_bps * best_tpb) { best_tpb = tpb; best_bps = bps; }
+        RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, path_kernel(rt::MODE_CULL, false, 5, false), tpb, smem));
+        if (bps * tpb > c->path_bps * c->path_tpb) { c->path_tpb = tpb; c->path_bps = bps; }
     }
+    if (c->path_bps < 1) return fail(RT_ERR_UNSUPPORTED, "rt_set_scene: path kernel does not fit on an SM with %zu B shared memory", cta_smem_bytes(n_pad, 256));
     if (best_bps < 1) return fail(RT_ERR_UNSUPPORTED, "rt_set_scene: render kernel does not fit on an SM with %zu B shared memory", cta_smem_bytes(n_pad, 256));
     c->tpb = best_tpb;
     c->render_blocks_per_sm = best_bps;
@@ -723,22 +791,16 @@ static int prepare_frames(rt_context* c, u64 first_sample, int spp, int max_dept
     p.first_sample = first_sample; p.spp = spp; p.max_depth = max_depth; p.flags = flags; p.seed = c->seed;
     p.exposure = static_cast<float>(std::pow(2, c->exposure_stops));          // spheres-app.cpp:174
     p.hdr = c->hdr(); p.work_counter = c->counters; p.stats = c->counters + 1;
-    // frame jitter Halton2D(n; 2,3) and lens samples HaltonSampleDisk(n+i+j; 4,5), spheres-app.cpp:140,152
+    // frame jitter Halton2D(n; 2,3) and lens samples HaltonSampleDisk(n+i+j; 4,5), spheres-app.cpp:140,152: built on the device,
+    // on the context's stream (no host table, no copy, no synchronisation: rt_render stays asynchronous)
     const size_t n_lens = static_cast<size_t>(spp) + c->W + c->H;
-    if (c->jitter_cap < static_cast<size_t>(spp)) { if (int r = dev_realloc(c->jitter, spp)) return r; c->jitter_cap = spp; }
-    if (c->lens_cap < n_lens) { if (int r = dev_realloc(c->lens, n_lens)) return r; c->lens_cap = n_lens; }
-    std::vector<float2> hj(spp), hl(n_lens);
-    for (int s = 0; s < spp; ++s) { const u64 n = first_sample + s; hj[s] = make_float2(host::halton(n, 2), host::halton(n, 3)); }
-    for (size_t k = 0; k < n_lens; ++k) {
-        const u64 idx = first_sample + k;
-        const float theta = RT_TWO_PI * host::halton(idx, 4);                 // quasi-random.cpp:54
-        const float r = host::halton(idx, 5);                                 // :55
-        float sn, cs; rt::sincos_pinned(theta, &sn, &cs);
-        hl[k] = make_float2(r * cs, r * sn);                                  // :57-60
+    if (c->jitter_cap < static_cast<size_t>(spp) || c->lens_cap < n_lens) {
+        RT_CUDA(cudaStreamSynchronize(c->stream));              // a previous launch may still read the tables being replaced (growth only)
+        if (c->jitter_cap < static_cast<size_t>(spp)) { const size_t cap = std::max<size_t>(spp, 2 * c->jitter_cap); if (int r = dev_realloc(c->jitter, cap)) return r; c->jitter_cap = cap; }
+        if (c->lens_cap < n_lens) { const size_t cap = std::max(n_lens, 2 * c->lens_cap); if (int r = dev_realloc(c->lens, cap)) return r; c->lens_cap = cap; }
     }
-    RT_CUDA(cudaMemcpyAsync(c->jitter, hj.data(), spp * sizeof(float2), cudaMemcpyHostToDevice, c->stream));
-    RT_CUDA(cudaMemcpyAsync(c->lens, hl.data(), n_lens * sizeof(float2), cudaMemcpyHostToDevice, c->stream));
-    RT_CUDA(cudaStreamSynchronize(c->stream));   // hj/hl are stack-owned pageable buffers
+    rt::rt_tables_kernel<<<static_cast<unsigned>((n_lens + 255) / 256), 256, 0, c->stream>>>(first_sample, spp, static_cast<int>(n_lens), c->jitter, c->lens);
+    ++c->launches;
     p.jitter = c->jitter; p.lens = c->lens;
     return RT_OK;
 }
@@ -782,47 +844,37 @@ static int render_wavefront(rt_context* c, const rt::RenderParams& p, uint32_t f
     return fail(RT_ERR_CUDA, "rt_render (wavefront): the work queue did not drain");
 }
 
-int rt_render(rt_context* c, uint64_t first_sample, int spp, int max_depth, uint32_t flags) {
-    if (!c) return fail(RT_ERR_INVALID_ARGUMENT, "rt_render: ctx is NULL");
-    if (!c->scene_set || !c->camera_set || !c->hdr()) return fail(RT_ERR_NOT_READY, "rt_render: scene, camera and framebuffer must be set first");
-    if (first_sample < 1 || spp < 0 || max_depth < 0) return fail(RT_ERR_INVALID_ARGUMENT, "rt_render: first_sample >= 1, spp >= 0, max_depth >= 0 required");
-    if (flags & ~(RT_FLAG_JITTER_OFF | RT_FLAG_LENS_OFF | RT_FLAG_WAVEFRONT | RT_FLAG_ACCEL | RT_FLAG_HALTON | RT_FLAG_DEBUG_NO_CULL_)) return fail(RT_ERR_INVALID_ARGUMENT, "rt_render: unknown flag bits 0x%x", flags);
-    if ((flags & RT_FLAG_HALTON) && (flags & (RT_FLAG_WAVEFRONT | RT_FLAG_ACCEL | RT_FLAG_DEBUG_NO_CULL_))) return fail(RT_ERR_INVALID_ARGUMENT, "rt_render: RT_FLAG_HALTON runs on the default brute-force megakernel only");
-    if ((flags & RT_FLAG_ACCEL) && (flags & (RT_FLAG_WAVEFRONT | RT_FLAG_DEBUG_NO_CULL_))) return fail(RT_ERR_INVALID_ARGUMENT, "rt_render: RT_FLAG_ACCEL cannot be combined with the wavefront layout or the no-cull debug mode");
-    if ((flags & RT_FLAG_ACCEL) && !c->accel_ok) return fail(RT_ERR_UNSUPPORTED, "rt_render: RT_FLAG_ACCEL unavailable for this scene: %s", c->accel_why.c_str());
-    if ((flags & RT_FLAG_WAVEFRONT) && max_depth >= (1 << 22)) return fail(RT_ERR_INVALID_ARGUMENT, "rt_render: the wavefront layout packs the depth into 23 bits");
-    if (spp == 0) return RT_OK;
-    if (int r = ctx_use(c)) return r;
-    rt::RenderParams p;
-    if (int r = prepare_frames(c, first_sample, spp, max_depth, flags, p)) return r;
-    // work items: (chunk of samples) x (pixel).  One chunk keeps the reference's sequential per-pixel sum order.
+// Switches the launch parameters to light k (k >= 1): that light alone, sky off, same paths; sample counts and the path /
+// closest-ray statistics come from light 0's launches.
+static void select_extra_light(const rt_context* c, int k, rt::RenderParams& p) {
+    const rt_context::ExtraLight& e = c->extra_lights[k - 1];
+    p.Lx = e.L[0]; p.Ly = e.L[1]; p.Lz = e.L[2]; p.lcx = e.lc[0]; p.lcy = e.lc[1]; p.lcz = e.lc[2];
+    p.iLx = e.iL[0]; p.iLy = e.iL[1]; p.iLz = e.iL[2]; p.cullC = e.cullC;
+    p.skyx = p.skyy = p.skyz = 0.f; p.primary_pass = 0;
+}
+static int ensure_partial(rt_context* c, size_t n_pix, int n_chunks) {
+    const size_t need = n_pix * static_cast<size_t>(n_chunks) * sizeof(float4);
+    if (c->partial_bytes < need) {
+        if (c->partial) { RT_CUDA(cudaStreamSynchronize(c->stream)); cudaFree(c->partial); c->partial = nullptr; c->partial_bytes = 0; }
+        RT_CUDA(cudaMalloc(&c->partial, need)); c->partial_bytes = need;
+    }
+    return RT_OK;
+}
+
+// Round-1 schedule (RT_FLAG_DEBUG_ONE_KERNEL, RT_FLAG_WAVEFRONT): one launch per light over the whole sample range.
+static int render_one_kernel(rt_context* c, rt::RenderParams& p, int spp, uint32_t flags) {
     int chunk = c->chunk_spp;
     if (chunk <= 0) { const int n_chunks = spp <= 16 ? 1 : std::min(16, spp / 8); chunk = (spp + n_chunks - 1) / n_chunks; }
     chunk = std::min(chunk, spp);
     p.chunk_spp = chunk; p.n_chunks = (spp + chunk - 1) / chunk;
     const size_t n_pix = static_cast<size_t>(c->W) * c->H;
     p.partial = nullptr;
-    if (p.n_chunks > 1) {
-        const size_t need = n_pix * p.n_chunks * sizeof(float4);
-        if (c->partial_bytes < need) {
-            if (c->partial) { cudaFree(c->partial); c->partial = nullptr; c->partial_bytes = 0; }
-            RT_CUDA(cudaMalloc(&c->partial, need)); c->partial_bytes = need;
-        }
-        p.partial = c->partial;
-    }
+    if (p.n_chunks > 1) { if (int r = ensure_partial(c, n_pix, p.n_chunks)) return r; p.partial = c->partial; }
     const size_t smem = cta_smem_bytes(c->n_pad, c->tpb);
     const int grid = c->prop.multiProcessorCount * c->render_blocks_per_sm;
-    if (!c->extra_lights.empty() && (flags & (RT_FLAG_WAVEFRONT | RT_FLAG_HALTON)))
-        return fail(RT_ERR_UNSUPPORTED, "rt_render: scenes with more than one light run on the megakernel with the counter RNG only (one launch per light over the same paths)");
-    EventPair ev = ev_begin(c, 0);
     const int n_launch_lights = 1 + static_cast<int>(c->extra_lights.size());
     for (int k = 0; k < n_launch_lights; ++k) {
-        if (k > 0) {                                     // light k alone, sky off, same paths; sample counts and path / closest-ray statistics come from pass 0
-            const rt_context::ExtraLight& e = c->extra_lights[k - 1];
-            p.Lx = e.L[0]; p.Ly = e.L[1]; p.Lz = e.L[2]; p.lcx = e.lc[0]; p.lcy = e.lc[1]; p.lcz = e.lc[2];
-            p.iLx = e.iL[0]; p.iLy = e.iL[1]; p.iLz = e.iL[2]; p.cullC = e.cullC;
-            p.skyx = p.skyy = p.skyz = 0.f; p.primary_pass = 0;
-        }
+        if (k > 0) select_extra_light(c, k, p);
         RT_CUDA(cudaMemsetAsync(c->counters, 0, sizeof(u64), c->stream));
         if (flags & RT_FLAG_WAVEFRONT) { if (int r = render_wavefront(c, p, flags)) return r; }
         else if (flags & RT_FLAG_ACCEL) {
@@ -839,11 +891,99 @@ int rt_render(rt_context* c, uint64_t first_sample, int spp, int max_depth, uint
             ++c->launches;
         }
         if (p.n_chunks > 1) {
-            rt::rt_combine_kernel<<<static_cast<unsigned>((n_pix + 255) / 256), 256, 0, c->stream>>>(p.hdr, p.partial, p.n_chunks, n_pix);
+            rt::rt_combine_kernel<<<static_cast<unsigned>((n_pix + 255) / 256), 256, 0, c->stream>>>(p.hdr, p.partial, p.n_chunks, n_pix, 0);
             ++c->launches;
         }
     }
-    ev_end(c, ev);
+    return RT_OK;
+}
+
+// Two-stage schedule (default): per batch of frames one first-hit launch, then one path launch per light.
+static int render_two_stage(rt_context* c, rt::RenderParams& p, int spp, int max_depth, uint32_t flags) {
+    const size_t n_pix = static_cast<size_t>(c->W) * c->H;
+    const bool accel = (flags & RT_FLAG_ACCEL) != 0, halton = (flags & RT_FLAG_HALTON) != 0;
+    const int mode = accel ? rt::MODE_ACCEL : (flags & RT_FLAG_DEBUG_NO_CULL_) ? rt::MODE_NO_CULL : rt::MODE_CULL;
+    const int gshift = accel ? p.accel.gshift : 5;
+    const bool direct = max_depth == 0 && !halton && mode != rt::MODE_NO_CULL;
+    const int tpb = accel ? c->accel_tpb : c->path_tpb, bps = accel ? c->accel_bps : c->path_bps;
+    const size_t smem = accel ? accel_cta_smem_bytes(p.accel, tpb) : cta_smem_bytes(c->n_pad, tpb);
+    const int grid = c->prop.multiProcessorCount * bps;
+    const void* k_first = first_hit_kernel(mode, gshift);
+    const void* k_path = path_kernel(mode, halton, gshift, direct);
+    // batch: as many frames as fit first-hit records of 512 MiB (2 B per pixel and frame), a multiple of 8, at most 4096
+    const size_t cap_bytes = 512ull << 20;
+    int batch = static_cast<int>(std::min<size_t>(4096, std::max<size_t>(8, (cap_bytes / (n_pix * 2)) & ~static_cast<size_t>(7))));
+    batch = std::min(batch, (spp + 7) & ~7);
+    const size_t hits_need = n_pix * static_cast<size_t>(batch) * sizeof(uint16_t);
+    if (c->hits_bytes < hits_need) {
+        if (c->hits) { RT_CUDA(cudaStreamSynchronize(c->stream)); cudaFree(c->hits); c->hits = nullptr; c->hits_bytes = 0; }
+        RT_CUDA(cudaMalloc(&c->hits, hits_need)); c->hits_bytes = hits_need;
+    }
+    p.hits = c->hits;
+    const int n_launch_lights = 1 + static_cast<int>(c->extra_lights.size());
+    const rt::RenderParams base = p;
+    const u64 lanes = static_cast<u64>(grid) * tpb;
+    for (int s0 = 0; s0 < spp; s0 += batch) {
+        p = base;
+        p.batch_s0 = s0; p.batch_n = std::min(batch, spp - s0); p.hit_stride = (p.batch_n + 7) & ~7;
+        // work items of stage 2: (pixel, chunk of the batch).  One chunk keeps the reference's sequential per-pixel sum order and
+        // needs no partial buffers; small images are split so that every lane sees >= ~16 items (load balance at the tail).
+        int chunk = c->chunk_spp > 0 ? ((c->chunk_spp + 7) & ~7) : 0;
+        if (chunk <= 0) {
+            const u64 want = std::max<u64>(1, (16 * lanes + n_pix - 1) / n_pix);
+            const int n_chunks = static_cast<int>(std::min<u64>(want, static_cast<u64>(p.hit_stride / 8)));
+            chunk = (((p.batch_n + n_chunks - 1) / n_chunks) + 7) & ~7;
+        }
+        p.chunk_spp = chunk; p.n_chunks = (p.batch_n + chunk - 1) / chunk;
+        p.partial = nullptr;
+        if (p.n_chunks > 1) { if (int r = ensure_partial(c, n_pix, p.n_chunks)) return r; p.partial = c->partial; }
+        void* args[] = {&p};
+        RT_CUDA(cudaLaunchKernel(k_first, dim3(grid), dim3(tpb), args, smem, c->stream));
+        ++c->launches;
+        // RT_FLAG_HALTON with several lights: the reference draws once per vertex and loops over the lights there (material.cpp:4-13);
+        // here light k re-walks the batch's paths, so the materials' indices are rewound to where light 0's pass found them and
+        // every pass draws the same numbers (exactly so when paths run one after another, as with the reference itself)
+        const bool rewind = halton && n_launch_lights > 1;
+        if (rewind) RT_CUDA(cudaMemcpyAsync(c->sampler + c->n_sampler, c->sampler, c->n_sampler * sizeof(u64), cudaMemcpyDeviceToDevice, c->stream));
+        for (int k = 0; k < n_launch_lights; ++k) {
+            if (k > 0) select_extra_light(c, k, p);
+            if (k > 0 && rewind) RT_CUDA(cudaMemcpyAsync(c->sampler, c->sampler + c->n_sampler, c->n_sampler * sizeof(u64), cudaMemcpyDeviceToDevice, c->stream));
+            p.overwrite = ((flags & RT_FLAG_OVERWRITE) && s0 == 0 && k == 0) ? 1 : 0;
+            RT_CUDA(cudaMemsetAsync(c->counters, 0, sizeof(u64), c->stream));
+            RT_CUDA(cudaLaunchKernel(k_path, dim3(grid), dim3(tpb), args, smem, c->stream));
+            ++c->launches;
+            if (p.n_chunks > 1) {
+                rt::rt_combine_kernel<<<static_cast<unsigned>((n_pix + 255) / 256), 256, 0, c->stream>>>(p.hdr, p.partial, p.n_chunks, n_pix, p.overwrite);
+                ++c->launches;
+            }
+        }
+    }
+    return RT_OK;
+}
+
+int rt_render(rt_context* c, uint64_t first_sample, int spp, int max_depth, uint32_t flags) {
+    if (!c) return fail(RT_ERR_INVALID_ARGUMENT, "rt_render: ctx is NULL");
+    if (!c->scene_set || !c->camera_set || !c->hdr()) return fail(RT_ERR_NOT_READY, "rt_render: scene, camera and framebuffer must be set first");
+    if (first_sample < 1 || spp < 0 || max_depth < 0) return fail(RT_ERR_INVALID_ARGUMENT, "rt_render: first_sample >= 1, spp >= 0, max_depth >= 0 required");
+    if (flags & ~(RT_FLAG_JITTER_OFF | RT_FLAG_LENS_OFF | RT_FLAG_WAVEFRONT | RT_FLAG_ACCEL | RT_FLAG_HALTON | RT_FLAG_OVERWRITE | RT_FLAG_DEBUG_NO_CULL_ | RT_FLAG_DEBUG_ONE_KERNEL_))
+        return fail(RT_ERR_INVALID_ARGUMENT, "rt_render: unknown flag bits 0x%x", flags);
+    const bool one_kernel = (flags & (RT_FLAG_WAVEFRONT | RT_FLAG_DEBUG_ONE_KERNEL_)) != 0;
+    if ((flags & RT_FLAG_HALTON) && (flags & (RT_FLAG_WAVEFRONT | RT_FLAG_DEBUG_NO_CULL_))) return fail(RT_ERR_INVALID_ARGUMENT, "rt_render: RT_FLAG_HALTON cannot be combined with the wavefront layout or the no-cull debug mode");
+    if ((flags & RT_FLAG_HALTON) && (flags & RT_FLAG_ACCEL) && one_kernel) return fail(RT_ERR_INVALID_ARGUMENT, "rt_render: RT_FLAG_HALTON with RT_FLAG_ACCEL runs on the two-stage schedule only");
+    if ((flags & RT_FLAG_ACCEL) && (flags & (RT_FLAG_WAVEFRONT | RT_FLAG_DEBUG_NO_CULL_))) return fail(RT_ERR_INVALID_ARGUMENT, "rt_render: RT_FLAG_ACCEL cannot be combined with the wavefront layout or the no-cull debug mode");
+    if ((flags & RT_FLAG_OVERWRITE) && one_kernel) return fail(RT_ERR_INVALID_ARGUMENT, "rt_render: RT_FLAG_OVERWRITE runs on the two-stage schedule only");
+    if ((flags & RT_FLAG_ACCEL) && !c->accel_ok) return fail(RT_ERR_UNSUPPORTED, "rt_render: RT_FLAG_ACCEL unavailable for this scene: %s", c->accel_why.c_str());
+    if ((flags & RT_FLAG_WAVEFRONT) && max_depth >= (1 << 22)) return fail(RT_ERR_INVALID_ARGUMENT, "rt_render: the wavefront layout packs the depth into 23 bits");
+    if (!c->extra_lights.empty() && (flags & RT_FLAG_WAVEFRONT))
+        return fail(RT_ERR_UNSUPPORTED, "rt_render: scenes with more than one light do not run on the wavefront layout");
+    if (spp == 0) return RT_OK;
+    if (int r = ctx_use(c)) return r;
+    rt::RenderParams p;
+    if (int r = prepare_frames(c, first_sample, spp, max_depth, flags, p)) return r;
+    EventPair ev = ev_begin(c, 0);
+    const int rc = one_kernel ? render_one_kernel(c, p, spp, flags) : render_two_stage(c, p, spp, max_depth, flags);
+    ev_end(c, ev);                                          // on every path: the pair goes back to the pool with the next collection
+    if (rc) return rc;
     RT_CUDA(cudaGetLastError());
     return RT_OK;
 }
@@ -912,10 +1052,12 @@ int rt_primary_hits(rt_context* c, uint64_t sample, uint32_t flags, int32_t* sph
     RT_CUDA(cudaStreamSynchronize(c->stream));
     return RT_OK;
 }
-int rt_scene_accel_image(const rt_scene* s, void* buf, size_t capacity, rt_accel_image_info* info) {
+int rt_scene_accel_image(const rt_scene* s, void* buf, size_t capacity, rt_accel_image_info* info) { return rt_scene_accel_image_slots(s, 0, buf, capacity, info); }
+int rt_scene_accel_image_slots(const rt_scene* s, int min_group_slots, void* buf, size_t capacity, rt_accel_image_info* info) {
     if (!s || !info) return fail(RT_ERR_INVALID_ARGUMENT, "rt_scene_accel_image: NULL argument");
+    if (gshift_of_slots(min_group_slots) < 0) return fail(RT_ERR_INVALID_ARGUMENT, "rt_scene_accel_image: min_group_slots must be 0, 8, 16 or 32");
     rt::AccelParams a; std::vector<unsigned char> img; std::string why;
-    if (!make_accel_image(s, a, img, why)) return fail(RT_ERR_UNSUPPORTED, "rt_scene_accel_image: RT_FLAG_ACCEL unavailable for this scene: %s", why.c_str());
+    if (!make_accel_image(s, a, img, why, gshift_of_slots(min_group_slots))) return fail(RT_ERR_UNSUPPORTED, "rt_scene_accel_image: RT_FLAG_ACCEL unavailable for this scene: %s", why.c_str());
     *info = rt_accel_image_info{};
     info->bytes = img.size();
     info->off_B = a.off_B; info->off_R = a.off_R; info->off_I = a.off_I; info->off_box = a.off_box; info->off_top = a.off_top;

@@ -85,26 +85,36 @@ __device__ __forceinline__ float4 lds128(uint32_t addr) {
 // Conservative discriminant signs of one sphere pair for both rays; as cull_pair() but (o-c).L is evaluated with three
 // FMAs from the centre instead of being read from a per-light array (the image carries no light-dependent data).
 struct CullRay2 { float ox2, oy2, oz2, ndx, ndy, ndz, nLx, nLy, nLz, noo, od, oL; };
+template <int RAYS>
 __device__ __forceinline__ void cull_pair2(const CullRay2& r, const float4 A, const float4 B, uint32_t& mc, uint32_t& ms) {
     const u64 cx = pk2(A.x, A.y), cy = pk2(A.z, A.w), cz = pk2(B.x, B.y);
     u64 nc2 = fadd2(pk2(B.z, B.w), bc2(r.noo));
     nc2 = ffma2(bc2(r.oz2), cz, nc2); nc2 = ffma2(bc2(r.oy2), cy, nc2); nc2 = ffma2(bc2(r.ox2), cx, nc2);
-    u64 b1 = ffma2(bc2(r.ndz), cz, bc2(r.od)); b1 = ffma2(bc2(r.ndy), cy, b1); b1 = ffma2(bc2(r.ndx), cx, b1);
-    u64 b2 = ffma2(bc2(r.nLz), cz, bc2(r.oL)); b2 = ffma2(bc2(r.nLy), cy, b2); b2 = ffma2(bc2(r.nLx), cx, b2);
-    const u64 d1 = ffma2(b1, b1, nc2);
-    const u64 d2 = ffma2(b2, b2, nc2);
     uint32_t lo, hi;
+    if constexpr ((RAYS & RAYS_CLOSEST) != 0) {
+        u64 b1 = ffma2(bc2(r.ndz), cz, bc2(r.od)); b1 = ffma2(bc2(r.ndy), cy, b1); b1 = ffma2(bc2(r.ndx), cx, b1);
+        const u64 d1 = ffma2(b1, b1, nc2);
 #if RT_CULL_DIRFILTER
-    uint32_t blo, bhi, nlo, nhi;                             // as cull_pair(): centre behind the origin and origin outside = miss
-    upk2(nc2, nlo, nhi);
-    upk2(d1, lo, hi); upk2(b1, blo, bhi); lo |= ~blo & nlo; hi |= ~bhi & nhi;
-    mc = __funnelshift_l(lo, mc, 1); mc = __funnelshift_l(hi, mc, 1);
-    upk2(d2, lo, hi); upk2(b2, blo, bhi); lo |= ~blo & nlo; hi |= ~bhi & nhi;
-    ms = __funnelshift_l(lo, ms, 1); ms = __funnelshift_l(hi, ms, 1);
+        uint32_t blo, bhi, nlo, nhi;                         // as cull_pair(): centre behind the origin and origin outside = miss
+        upk2(nc2, nlo, nhi);
+        upk2(d1, lo, hi); upk2(b1, blo, bhi); lo |= ~blo & nlo; hi |= ~bhi & nhi;
 #else
-    upk2(d1, lo, hi); mc = __funnelshift_l(lo, mc, 1); mc = __funnelshift_l(hi, mc, 1);
-    upk2(d2, lo, hi); ms = __funnelshift_l(lo, ms, 1); ms = __funnelshift_l(hi, ms, 1);
+        upk2(d1, lo, hi);
 #endif
+        mc = __funnelshift_l(lo, mc, 1); mc = __funnelshift_l(hi, mc, 1);
+    }
+    if constexpr ((RAYS & RAYS_SHADOW) != 0) {
+        u64 b2 = ffma2(bc2(r.nLz), cz, bc2(r.oL)); b2 = ffma2(bc2(r.nLy), cy, b2); b2 = ffma2(bc2(r.nLx), cx, b2);
+        const u64 d2 = ffma2(b2, b2, nc2);
+#if RT_CULL_DIRFILTER
+        uint32_t blo, bhi, nlo, nhi;
+        upk2(nc2, nlo, nhi);
+        upk2(d2, lo, hi); upk2(b2, blo, bhi); lo |= ~blo & nlo; hi |= ~bhi & nhi;
+#else
+        upk2(d2, lo, hi);
+#endif
+        ms = __funnelshift_l(lo, ms, 1); ms = __funnelshift_l(hi, ms, 1);
+    }
 }
 
 // Slab test constants of one ray.  A box (centre c, half extent h) is touched when, per axis k,
@@ -150,7 +160,7 @@ struct AccelCounters { uint32_t group_visits; };
 
 // Same contract as fused_query(): closest hit along (o,d) and occlusion along (o,L).  res.idx is the ORIGINAL sphere
 // index, res.slot the position in the re-ordered image (for the hit record's centre / radius).
-template <int GSHIFT>
+template <int GSHIFT, int RAYS = RAYS_BOTH>
 __device__ __forceinline__ QueryResult fused_query_accel(const AccelSmem& s, const AccelParams& a, int lstride,
                                                          V3 o, V3 d, V3 L, V3 invL, bool want_closest, bool want_shadow, AccelCounters& cnt) {
     QueryResult res; res.t = 0.f; res.idx = -1; res.slot = -1; res.occluded = false;
@@ -168,6 +178,8 @@ __device__ __forceinline__ QueryResult fused_query_accel(const AccelSmem& s, con
     ex.a = dot3(d, d);
     ex.aL = dot3(L, L);
     ex.ra = rcp_refined(ex.a); ex.raL = rcp_refined(ex.aL);
+    if constexpr ((RAYS & RAYS_CLOSEST) == 0) want_closest = false;
+    if constexpr ((RAYS & RAYS_SHADOW) == 0) want_shadow = false;
     const uint32_t en_c = want_closest ? 0xffffffffu : 0u;
     uint32_t en_s = want_shadow ? 0xffffffffu : 0u;
     uint32_t* const gm = s.scratch;                                   // one byte per L2 node
@@ -196,8 +208,8 @@ __device__ __forceinline__ QueryResult fused_query_accel(const AccelSmem& s, con
     if (!flat) {
         for (int j = 0; j < a.n2; ++j) {
             const float4 b0 = s.top[2 * j], b1 = s.top[2 * j + 1];
-            const bool hc = box_touched(rc, b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, neg_t_slack);
-            const bool hs = box_touched(rs, b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, neg_t_slack);
+            const bool hc = (RAYS & RAYS_CLOSEST) && box_touched(rc, b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, neg_t_slack);
+            const bool hs = (RAYS & RAYS_SHADOW) && box_touched(rs, b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, neg_t_slack);
             if (hc | hs) m2 |= 1u << j;
         }
     }
@@ -216,8 +228,8 @@ __device__ __forceinline__ QueryResult fused_query_accel(const AccelSmem& s, con
             const float hxa[4] = {hx.x, hx.y, hx.z, hx.w}, hya[4] = {hy.x, hy.y, hy.z, hy.w}, hza[4] = {hz.x, hz.y, hz.z, hz.w};
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
-                const bool hc = box_touched(rc, cxa[k], cya[k], cza[k], hxa[k], hya[k], hza[k], neg_t_slack);
-                const bool hs = box_touched(rs, cxa[k], cya[k], cza[k], hxa[k], hya[k], hza[k], neg_t_slack);
+                const bool hc = (RAYS & RAYS_CLOSEST) && box_touched(rc, cxa[k], cya[k], cza[k], hxa[k], hya[k], hza[k], neg_t_slack);
+                const bool hs = (RAYS & RAYS_SHADOW) && box_touched(rs, cxa[k], cya[k], cza[k], hxa[k], hya[k], hza[k], neg_t_slack);
                 if (hc | hs) byte |= 1u << (h * 4 + k);
             }
         }
@@ -237,7 +249,7 @@ __device__ __forceinline__ QueryResult fused_query_accel(const AccelSmem& s, con
         const int np_g = min(16, a.n_big_pairs - 16 * bg);
         uint32_t mc = 0u, ms = 0u;
 #pragma unroll 2
-        for (int q = 0; q < np_g; ++q) cull_pair2(cr, s.sA[bg * 16 + q], s.sB[bg * 16 + q], mc, ms);
+        for (int q = 0; q < np_g; ++q) cull_pair2<RAYS>(cr, s.sA[bg * 16 + q], s.sB[bg * 16 + q], mc, ms);
         const uint32_t valid = 0xffffffffu << (32 - 2 * np_g);           // bit 31 = first sphere of the group, as everywhere
         const uint32_t cc = ~(mc << (32 - 2 * np_g)) & valid & en_c, cs = ~(ms << (32 - 2 * np_g)) & valid & en_s;
         if (cc) { ent[(2 * ne) * lstride] = cc; ent[(2 * ne + 1) * lstride] = static_cast<uint32_t>(bg * 32); ++ne; }
@@ -263,7 +275,7 @@ __device__ __forceinline__ QueryResult fused_query_accel(const AccelSmem& s, con
             const uint32_t pb = sb32 + static_cast<uint32_t>(slot_base) * 8u + (static_cast<uint32_t>(rot) << 4);
             uint32_t mc = 0u, ms = 0u;
 #pragma unroll
-            for (int q = 0; q < kPPG; ++q) cull_pair2(cr, lds128(pa ^ (q << 4)), lds128(pb ^ (q << 4)), mc, ms);
+            for (int q = 0; q < kPPG; ++q) cull_pair2<RAYS>(cr, lds128(pa ^ (q << 4)), lds128(pb ^ (q << 4)), mc, ms);
             // bit 31 = first slot of the group, as everywhere; a group smaller than 32 slots leaves the low bits clear
             const uint32_t gvalid = 0xffffffffu << (32 - kGS);
             const uint32_t cc = ~(mc << (32 - kGS)) & gvalid & en_c, cs = ~(ms << (32 - kGS)) & gvalid & en_s;

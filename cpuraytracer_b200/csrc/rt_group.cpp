@@ -144,17 +144,19 @@ int rt_group_synchronize(rt_group* g) { FOR_MEMBERS(rt_synchronize(mb.ctx)); }
 int rt_group_render(rt_group* g, uint64_t first_sample, int spp, int max_depth, uint32_t flags) {
     if (!g) return gfail(RT_ERR_INVALID_ARGUMENT, "rt_group_render: group is NULL");
     const int n = static_cast<int>(g->m.size());
-    // 1. every member renders its disjoint frame range into its own running sum.  Members 1.. start from zero so that
-    //    after the reduce member 0 holds (previous total + this call), exactly what one GPU would hold.
+    // 1. every member renders its disjoint frame range into its own running sum.  Members 1.. START their sum with this call
+    //    (RT_FLAG_OVERWRITE: no clear, the old content is not read; a clear where the schedule cannot overwrite or the member
+    //    has no frames) so that after the reduce member 0 holds (previous total + this call), exactly what one GPU would hold.
     for (int i = 0; i < n; ++i) {
         Member& mb = g->m[i];
         uint64_t my_first; int my_spp;
         if (int rc = rt_group_shard(first_sample, spp, i, n, &my_first, &my_spp)) return rc;
         G_CUDA(cudaSetDevice(mb.device));
         cudaStream_t st = static_cast<cudaStream_t>(rt_get_stream(mb.ctx));
-        if (i > 0) { if (int rc = rt_framebuffer_clear(mb.ctx)) return forward(rc); }
+        const bool can_overwrite = i > 0 && my_spp > 0 && !(flags & (RT_FLAG_WAVEFRONT | RT_FLAG_DEBUG_ONE_KERNEL));
+        if (i > 0 && !can_overwrite) { if (int rc = rt_framebuffer_clear(mb.ctx)) return forward(rc); }
         G_CUDA(cudaEventRecord(mb.e0, st));
-        if (my_spp > 0) { if (int rc = rt_render(mb.ctx, my_first, my_spp, max_depth, flags)) return forward(rc); }
+        if (my_spp > 0) { if (int rc = rt_render(mb.ctx, my_first, my_spp, max_depth, flags | (can_overwrite ? RT_FLAG_OVERWRITE : 0u))) return forward(rc); }
         G_CUDA(cudaEventRecord(mb.e1, st));
     }
     // 2. one ncclReduce(sum) of the float4 buffers onto member 0, on the render streams (in place on the root)

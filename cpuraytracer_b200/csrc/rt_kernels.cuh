@@ -40,6 +40,12 @@ struct RenderParams {
     float iLx, iLy, iLz;         // safe_inv of the light direction (slab test of the shadow ray)
     int primary_pass;            // 1: this launch owns the sample count and the path / closest-ray statistics; 0: an additional light's pass over the same paths
     u64* sampler;                // RT_FLAG_HALTON: [n_materials][2] = (m_reflectionProbabilitySampleIndex, m_sampleIndex), material.h:34,50-51,67
+    // two-stage schedule (rt_first_hit_kernel + rt_path_kernel): one launch pair renders the batch of frames
+    // [first_sample + batch_s0, first_sample + batch_s0 + batch_n); chunk_spp / n_chunks then split the BATCH into work items
+    uint16_t* hits;              // [W*H][hit_stride]: slot + 1 of the sphere the primary ray of (pixel, batch sample) hits, 0 = sky
+    int hit_stride;              // samples per row: batch_n rounded up to a multiple of 8 (rows are 16-byte aligned)
+    int batch_s0, batch_n;
+    int overwrite;               // 1: this launch starts the running sum (no read of hdr): RT_FLAG_OVERWRITE, first batch of the call
 };
 
 #define RT_FLAG_JITTER_OFF_ 1u
@@ -47,7 +53,9 @@ struct RenderParams {
 #define RT_FLAG_WAVEFRONT_ 4u
 #define RT_FLAG_ACCEL_ 8u
 #define RT_FLAG_HALTON_ 16u
+#define RT_FLAG_OVERWRITE_ 32u
 #define RT_FLAG_DEBUG_NO_CULL_ 0x100u
+#define RT_FLAG_DEBUG_ONE_KERNEL_ 0x200u   /* round-1 schedule: primary rays inside the path megakernel (kept for the measured comparison) */
 
 enum LaneState { ST_NEED_ITEM = 0, ST_NEW_PATH = 1, ST_IN_PATH = 2, ST_DONE = 3 };
 
@@ -130,9 +138,16 @@ __device__ __forceinline__ bool scatter(const DevMat& m, V3 d, V3 pos, V3 n, V3 
         out_d = normalize3((dir.x * b1 + dir.y * b2) + dir.z * n);             // :55-56
         return true;
     }
-    if (m.kind == 1) {                                                         // Metal: always reflects (alpha lane, :81-85)
+    if (m.kind == 1) {                                                         // Metal
         const float ndv = dot3(neg3(d), n);
         if (!(ndv > 0.f)) return false;                                        // :74
+        // :77-85: reflectance = f0 + (1 - f0) (1 - n.v)^5 on all FOUR lanes of the texture colour, reflect when ANY lane exceeds
+        // the random number.  Lane w is the texture's alpha: with alpha == 1 that lane is exactly 1 > xi, i.e. always.
+        const float alpha = texture_alpha(m, 0.5f * n.x + 0.5f, 0.5f * n.z + 0.5f);
+        if (alpha != 1.0f) {
+            const float nv = saturate1(ndv);
+            if (!(schlick(tex.x, nv) > xi || schlick(tex.y, nv) > xi || schlick(tex.z, nv) > xi || schlick(alpha, nv) > xi)) return false;
+        }
         atten = tex;                                                           // :87
         out_d = mirror;                                                        // :89
         return true;
@@ -334,11 +349,275 @@ __global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : RT_MAX
     }
 }
 
+// ------------------------------------------------------------------------------------------------------------------
+// Two-stage schedule (default since round 2).  Measured on the one-kernel megakernel above (profiles/r01y_*): 42 % of all
+// fused passes carry a PRIMARY ray -- a closest-only query whose shadow half idles -- and after every pass only ~55 % of
+// the lanes have a hit to shade (most paths end in the sky), so the shading code runs at ~12 of 32 threads.  Stage 1 traces
+// all primary rays of a batch of frames on their own: warps of 8x4 pixel tiles, coherent rays, closest-only cull (8 instead
+// of 10 packed FP ops per sphere pair, no per-light array), no shading code, and leaves one 16-bit record per (pixel, sample):
+// the slot of the sphere hit, or 0 for the sky.  Stage 2 is the path megakernel with regeneration FROM those records: sky
+// samples are accumulated without a query, and a regenerated path arrives with a hit in hand, so the single shading block
+// of the loop serves the query's hits AND the regenerated primary hits (~30 of 32 lanes busy instead of ~17).
+// Arithmetic per path is unchanged (same device functions, same order), so the bits are those of the one-kernel schedule.
+// ------------------------------------------------------------------------------------------------------------------
+
+// Stage 1.  Work item of a WARP = (8x4 pixel tile, group of 8 consecutive batch samples); static round-robin over the grid.
+template <int MODE, int GSHIFT = 5>
+__global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : RT_MAX_TPB) rt_first_hit_kernel(const RenderParams p) {
+    extern __shared__ __align__(256) unsigned char smem[];
+    float4 *sA = nullptr, *sB = nullptr; float2* sC = nullptr; float* sR = nullptr; uint32_t* lists = nullptr;
+    AccelSmem av{};
+    if constexpr (MODE == MODE_ACCEL) av = stage_accel(p.accel, smem);
+    else stage_scene(p, sA, sB, sC, sR, lists, smem);
+    AccelCounters acnt; acnt.group_visits = 0u;
+    const unsigned FULL = 0xffffffffu;
+    const unsigned lane = threadIdx.x & 31u;
+    const V3 Ldir = mk3(p.Lx, p.Ly, p.Lz);
+    const u64 n_tiles = static_cast<u64>(p.tiles_x) * p.tiles_y;
+    const u64 n_items = n_tiles * static_cast<u64>(p.hit_stride >> 3);
+    const u64 n_warps = (static_cast<u64>(gridDim.x) * blockDim.x) >> 5;
+    uint32_t n_closest = 0, n_pass = 0;
+    for (u64 item = (static_cast<u64>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5; item < n_items; item += n_warps) {
+        const uint32_t tile = static_cast<uint32_t>(item % n_tiles);
+        const int g = static_cast<int>(item / n_tiles);
+        const int px = static_cast<int>((tile % p.tiles_x) * 8u + (lane & 7u));
+        const int py = static_cast<int>((tile / p.tiles_x) * 4u + (lane >> 3));
+        const bool valid = px < p.W && py < p.H;
+        u64 rec_lo = 0ull, rec_hi = 0ull;
+#pragma unroll 1
+        for (int k = 0; k < 8; ++k) {
+            const int sb = g * 8 + k;                        // sample index inside the batch
+            if (sb >= p.batch_n) break;                      // warp-uniform
+            const int s = p.batch_s0 + sb;                   // index into the per-call Halton tables
+            V3 o = mk3(0.f, 0.f, 0.f), d = mk3(0.f, 0.f, 1.f);
+            if (valid) {
+                float jx = 0.f, jy = 0.f, lx = 0.f, ly = 0.f;
+                if (!(p.flags & RT_FLAG_JITTER_OFF_)) { const float2 j = __ldg(&p.jitter[s]); jx = j.x; jy = j.y; }
+                if (!(p.flags & RT_FLAG_LENS_OFF_)) { const float2 l = __ldg(&p.lens[s + px + py]); lx = l.x; ly = l.y; }
+                const float u = div_rn(static_cast<float>(px) + jx, static_cast<float>(p.W));   // spheres-app.cpp:149
+                const float v = div_rn(static_cast<float>(py) + jy, static_cast<float>(p.H));   // :150
+                camera_get_ray(p.cam, u, v, lx, ly, o, d);
+                ++n_closest;
+            }
+            QueryResult q;
+            if constexpr (MODE == MODE_ACCEL) q = fused_query_accel<GSHIFT, RAYS_CLOSEST>(av, p.accel, static_cast<int>(blockDim.x), o, d, Ldir, mk3(p.iLx, p.iLy, p.iLz), valid, false, acnt);
+            else q = fused_query<MODE == MODE_NO_CULL, RAYS_CLOSEST>(sA, sB, sC, sR, lists, static_cast<int>(blockDim.x), p.n_groups, p.n_spheres, o, d, Ldir, valid, false);
+            ++n_pass;
+            const u64 v16 = (valid && q.idx >= 0) ? static_cast<u64>(((MODE == MODE_ACCEL) ? q.slot : q.idx) + 1) : 0ull;
+            if (k < 4) rec_lo |= v16 << (16 * k); else rec_hi |= v16 << (16 * (k - 4));
+        }
+        if (valid) {
+            const size_t pix = static_cast<size_t>(py) * p.W + px;
+            uint4 r; r.x = static_cast<uint32_t>(rec_lo); r.y = static_cast<uint32_t>(rec_lo >> 32); r.z = static_cast<uint32_t>(rec_hi); r.w = static_cast<uint32_t>(rec_hi >> 32);
+            *reinterpret_cast<uint4*>(p.hits + pix * p.hit_stride + static_cast<size_t>(g) * 8) = r;
+        }
+    }
+    u64 c0 = n_closest;
+    u64 c5 = (MODE == MODE_ACCEL) ? static_cast<u64>(p.accel.n_big_pairs * 2) * n_closest + static_cast<u64>(1 << GSHIFT) * acnt.group_visits
+                                  : static_cast<u64>(p.n_spheres) * n_closest;
+    for (int off = 16; off > 0; off >>= 1) { c0 += __shfl_down_sync(FULL, c0, off); c5 += __shfl_down_sync(FULL, c5, off); }
+    if (lane == 0) { atomicAdd(&p.stats[0], c0); atomicAdd(&p.stats[2], static_cast<u64>(n_pass)); atomicAdd(&p.stats[5], c5); }
+}
+
+// Stage 2.  One thread = one path at a time; work item of a lane = (pixel, chunk of the batch's samples), handed out by a
+// warp-aggregated atomicAdd as in the one-kernel schedule.  Lane states:
+//   NEED_ITEM -> SCAN (walk the pixel's first-hit records in sample order: a sky sample is accumulated on the spot, a hit
+//   sample becomes a path) -> HIT_NEW (primary ray regenerated, t recomputed by the same exact test stage 1 ran) -> SHADE
+//   (K4 at the vertex in hand) -> QUERY (fused closest + shadow pass) -> SHADE (hit) | SCAN (path complete) ... -> DONE.
+// DIRECT_ONLY (max_depth == 0, BASELINE configs[1]): no lane ever asks for a closest hit here, the pass is shadow-only.
+enum PathLaneState { PS_NEED_ITEM = 0, PS_SCAN = 1, PS_HIT_NEW = 2, PS_SHADE = 3, PS_QUERY = 4, PS_DONE = 5 };
+template <int MODE, bool HALTON = false, int GSHIFT = 5, bool DIRECT_ONLY = false>
+__global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : RT_MAX_TPB) rt_path_kernel(const RenderParams p) {
+    extern __shared__ __align__(256) unsigned char smem[];
+    float4 *sA = nullptr, *sB = nullptr; float2* sC = nullptr; float* sR = nullptr; uint32_t* lists = nullptr;
+    AccelSmem av{};
+    if constexpr (MODE == MODE_ACCEL) {
+        av = stage_accel(p.accel, smem);
+        sA = const_cast<float4*>(av.sA); sB = const_cast<float4*>(av.sB); sR = const_cast<float*>(av.sR);
+    } else stage_scene(p, sA, sB, sC, sR, lists, smem);
+    const int lstride = static_cast<int>(blockDim.x);
+    const V3 invL = mk3(p.iLx, p.iLy, p.iLz);
+    AccelCounters acnt; acnt.group_visits = 0u;
+    constexpr int kRays = DIRECT_ONLY ? RAYS_SHADOW : RAYS_BOTH;
+
+    const unsigned FULL = 0xffffffffu;
+    const unsigned lane = threadIdx.x & 31u;
+    const u64 n_items = static_cast<u64>(p.tiles_x) * p.tiles_y * 32ull * static_cast<u64>(p.n_chunks);
+    const size_t n_pix = static_cast<size_t>(p.W) * p.H;
+    const V3 Ldir = mk3(p.Lx, p.Ly, p.Lz);
+    const V3 sky = mk3(p.skyx, p.skyy, p.skyz);
+    const bool has_light = p.n_lights > 0;
+
+    int st = PS_NEED_ITEM;
+    int pix = 0, px = 0, py = 0, chunk = 0, s_cur = 0, s_end = 0, depth = 0, hit_slot = 0;
+    float hit_t = 0.f;
+    uint4 rec = make_uint4(0u, 0u, 0u, 0u);                 // first-hit records of batch samples [s_cur & ~7, +8) of this pixel
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    V3 o = mk3(0.f, 0.f, 0.f), d = mk3(0.f, 0.f, 1.f);
+    V3 T = mk3(1.f, 1.f, 1.f), Lsum = mk3(0.f, 0.f, 0.f), pend = mk3(0.f, 0.f, 0.f);
+    bool want_closest = false, want_shadow = false;
+    uint32_t n_closest = 0, n_shadow = 0, n_pass = 0, n_paths = 0, n_skip = 0;
+
+    for (;;) {
+        // ---- regeneration: work items (warp-aggregated fetch) and the walk over the pixel's first-hit records ----
+        for (;;) {
+            const unsigned need = __ballot_sync(FULL, st == PS_NEED_ITEM);
+            if (need) {
+                const int leader = __ffs(need) - 1;
+                u64 base = 0;
+                if (static_cast<int>(lane) == leader) base = atomicAdd(p.work_counter, static_cast<u64>(__popc(need)));
+                base = __shfl_sync(FULL, base, leader);
+                if (st == PS_NEED_ITEM) {
+                    const u64 item = base + __popc(need & ((1u << lane) - 1u));
+                    if (item >= n_items) st = PS_DONE;
+                    else if (item_to_pixel(p, item, chunk, px, py)) {
+                        pix = py * p.W + px;
+                        s_cur = chunk * p.chunk_spp;                         // chunk_spp is a multiple of 8: records stay aligned
+                        s_end = min(p.batch_n, s_cur + p.chunk_spp);
+                        acc = (p.n_chunks == 1 && !p.overwrite) ? p.hdr[pix] : make_float4(0.f, 0.f, 0.f, 0.f);
+                        st = PS_SCAN;
+                    }
+                }
+            }
+            if (st == PS_SCAN) {
+                for (;;) {
+                    if (s_cur >= s_end) {
+                        if (p.n_chunks == 1) p.hdr[pix] = acc;
+                        else p.partial[static_cast<size_t>(chunk) * n_pix + pix] = acc;
+                        st = PS_NEED_ITEM;
+                        break;
+                    }
+                    if ((s_cur & 7) == 0) rec = __ldg(reinterpret_cast<const uint4*>(p.hits + static_cast<size_t>(pix) * p.hit_stride + s_cur));
+                    const int f = s_cur & 7;
+                    const uint32_t w = (f < 2) ? rec.x : (f < 4) ? rec.y : (f < 6) ? rec.z : rec.w;
+                    const uint32_t v16 = (w >> (16 * (f & 1))) & 0xffffu;
+                    if (v16) { hit_slot = static_cast<int>(v16) - 1; st = PS_HIT_NEW; break; }
+                    // the primary ray left the scene: Lsum = T * sky with T = 1 (spheres-app.cpp:255), then :182-183
+                    acc.x += sky.x * p.exposure; acc.y += sky.y * p.exposure; acc.z += sky.z * p.exposure;
+                    if (p.primary_pass) { acc.w += 1.0f; ++n_paths; }
+                    ++s_cur;
+                }
+            }
+            if (!__any_sync(FULL, st == PS_NEED_ITEM)) break;
+        }
+        if (__all_sync(FULL, st == PS_DONE)) break;
+
+        // ---- K1 again for the regenerated paths: the primary ray of (pixel, sample) and the t stage 1 found on that sphere ----
+        if (st == PS_HIT_NEW) {
+            const int s = p.batch_s0 + s_cur;
+            float jx = 0.f, jy = 0.f, lx = 0.f, ly = 0.f;
+            if (!(p.flags & RT_FLAG_JITTER_OFF_)) { const float2 j = __ldg(&p.jitter[s]); jx = j.x; jy = j.y; }
+            if (!(p.flags & RT_FLAG_LENS_OFF_)) { const float2 l = __ldg(&p.lens[s + px + py]); lx = l.x; ly = l.y; }
+            const float u = div_rn(static_cast<float>(px) + jx, static_cast<float>(p.W));
+            const float v = div_rn(static_cast<float>(py) + jy, static_cast<float>(p.H));
+            camera_get_ray(p.cam, u, v, lx, ly, o, d);
+            const float* fa = reinterpret_cast<const float*>(sA) + (hit_slot >> 1) * 4 + (hit_slot & 1);
+            const float a = dot3(d, d);
+            hit_t = 0.f;
+            sphere_exact(fa[0], fa[2], reinterpret_cast<const float*>(sB)[(hit_slot >> 1) * 4 + (hit_slot & 1)], sR[hit_slot], o, d, a, rcp_refined(a), false, hit_t);
+            T = mk3(1.f, 1.f, 1.f); Lsum = mk3(0.f, 0.f, 0.f);
+            depth = 0; want_shadow = false;
+            st = PS_SHADE;
+        }
+
+        // ---- K4 at the vertex in hand (a query hit of the last pass, or a regenerated primary hit) ----
+        if (st == PS_SHADE) {
+            const int slot = hit_slot;
+            int idx = slot;
+            if constexpr (MODE == MODE_ACCEL) idx = av.sI[slot];
+            const float* fa = reinterpret_cast<const float*>(sA) + (slot >> 1) * 4 + (slot & 1);
+            const V3 ctr = mk3(fa[0], fa[2], reinterpret_cast<const float*>(sB)[(slot >> 1) * 4 + (slot & 1)]);
+            const float radius = sR[slot];
+            const V3 pos = mk3(hit_t * d.x + o.x, hit_t * d.y + o.y, hit_t * d.z + o.z);   // ray-tracing.cpp:61
+            const V3 n = (pos - ctr) / radius;                                   // :62
+            const float tu = 0.5f * n.x + 0.5f, tv = 0.5f * n.z + 0.5f;          // :36-37
+            const DevMat m = p.mats[idx];
+            const V3 tex = texture_rgb(m, tu, tv);                               // texture.cpp:8-33, once per hit
+            const bool cont = depth < p.max_depth;                               // spheres-app.cpp:247
+            V3 atten = mk3(0.f, 0.f, 0.f), nd = d;
+            bool scattered = false;
+            if (cont || HALTON) {                                                // the reference scatters before it tests the depth (:246-247)
+                float xi, u1, u2;
+                if constexpr (HALTON) draw_halton(m, p.sampler, d, n, xi, u1, u2);
+                else rng_counter(static_cast<uint32_t>(pix), p.first_sample + static_cast<u64>(p.batch_s0 + s_cur), static_cast<uint32_t>(depth), p.seed, xi, u1, u2);
+                scattered = scatter(m, d, pos, n, tex, xi, u1, u2, atten, nd);      // :246
+            }
+            want_shadow = false;
+            if (has_light) {                                                     // :250
+                const float n_dot_l = saturate1(dot3(n, Ldir));                  // light.cpp:26
+                if (n_dot_l > 0.f) { pend = T * direct_unshadowed(p, m, pos, n, tex, n_dot_l); want_shadow = true; }
+                else { ++n_shadow; ++n_skip; }   // facing away: radianceIn == 0 (light.cpp:27), so the term is 0 whether or not the
+                                     // reference's shadow ray (:13-15) is occluded; the ray is counted, not traced
+            }
+            o = pos;
+            want_closest = cont && scattered;
+            if (want_closest) { T = T * atten; d = nd; ++depth; }                // :251
+            st = PS_QUERY;
+        }
+
+        // ---- K2+K3: fused closest-hit / shadow query ----
+        const bool active = (st == PS_QUERY);
+        QueryResult q;
+        if constexpr (MODE == MODE_ACCEL) q = fused_query_accel<GSHIFT, kRays>(av, p.accel, lstride, o, d, Ldir, invL, active && want_closest, active && want_shadow, acnt);
+        else q = fused_query<MODE == MODE_NO_CULL, kRays>(sA, sB, sC, sR, lists, lstride, p.n_groups, p.n_spheres, o, d, Ldir, active && want_closest, active && want_shadow);
+        ++n_pass;
+
+        // ---- resolve the pass ----
+        if (active) {
+            if (want_shadow) { ++n_shadow; if (!q.occluded) Lsum = Lsum + pend; }        // light.cpp:15-19
+            want_shadow = false;
+            bool complete = true;
+            if (want_closest) {
+                ++n_closest;
+                if (q.idx < 0) Lsum = Lsum + T * sky;                                    // spheres-app.cpp:255
+                else { hit_slot = (MODE == MODE_ACCEL) ? q.slot : q.idx; hit_t = q.t; st = PS_SHADE; complete = false; }
+                want_closest = false;
+            }
+            if (complete) {
+                acc.x += Lsum.x * p.exposure; acc.y += Lsum.y * p.exposure; acc.z += Lsum.z * p.exposure;   // :182-183
+                if (p.primary_pass) { acc.w += 1.0f; ++n_paths; }
+                ++s_cur;
+                st = PS_SCAN;
+            }
+        }
+    }
+
+    // ---- stats: warp reduce, one atomic per warp (primary rays were counted by stage 1) ----
+    u64 c0 = p.primary_pass ? n_closest : 0u, c1 = n_shadow, c3 = n_paths, c4 = n_skip;
+    u64 c5 = (MODE == MODE_ACCEL)
+        ? static_cast<u64>(p.accel.n_big_pairs * 2) * (n_closest + n_shadow - n_skip) + static_cast<u64>(1 << GSHIFT) * acnt.group_visits
+        : static_cast<u64>(p.n_spheres) * (n_closest + n_shadow - n_skip);
+    for (int off = 16; off > 0; off >>= 1) {
+        c0 += __shfl_down_sync(FULL, c0, off); c1 += __shfl_down_sync(FULL, c1, off); c3 += __shfl_down_sync(FULL, c3, off);
+        c4 += __shfl_down_sync(FULL, c4, off); c5 += __shfl_down_sync(FULL, c5, off);
+    }
+    if (lane == 0) {
+        atomicAdd(&p.stats[0], c0); atomicAdd(&p.stats[1], c1); atomicAdd(&p.stats[2], static_cast<u64>(n_pass)); atomicAdd(&p.stats[3], c3);
+        atomicAdd(&p.stats[4], c4); atomicAdd(&p.stats[5], c5);
+    }
+}
+
+// Per-call Halton tables on the device (no host table, no pageable copy, no stream synchronisation in rt_render):
+// jitter[s] = Halton2D(first + s; 2, 3) (spheres-app.cpp:140), lens[k] = HaltonSampleDisk(first + k; 4, 5) (:152,
+// quasi-random.cpp:52-61).  Same operations in the same order as the host restatement they replace (IEEE division, no
+// contraction), so the primary rays are bit-identical to the reference's for every frame index.
+__global__ void rt_tables_kernel(u64 first_sample, int n_jitter, int n_lens, float2* __restrict__ jitter, float2* __restrict__ lens) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n_jitter) { const u64 n = first_sample + static_cast<u64>(i); jitter[i] = make_float2(halton_sample(n, 2), halton_sample(n, 3)); }
+    if (i < n_lens) {
+        const u64 n = first_sample + static_cast<u64>(i);
+        const float theta = RT_TWO_PI * halton_sample(n, 4);                 // quasi-random.cpp:54
+        const float r = halton_sample(n, 5);                                 // :55
+        float sn, cs; sincos_pinned(theta, &sn, &cs);
+        lens[i] = make_float2(r * cs, r * sn);                               // :57-60
+    }
+}
+
 // hdr[p] = ((hdr[p] + partial[0][p]) + partial[1][p]) + ...   (fixed order => deterministic)
-__global__ void rt_combine_kernel(float4* __restrict__ hdr, const float4* __restrict__ partial, int n_chunks, size_t n_pixels) {
+__global__ void rt_combine_kernel(float4* __restrict__ hdr, const float4* __restrict__ partial, int n_chunks, size_t n_pixels, int overwrite) {
     const size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x;
     if (i >= n_pixels) return;
-    float4 a = hdr[i];
+    float4 a = overwrite ? make_float4(0.f, 0.f, 0.f, 0.f) : hdr[i];
     for (int c = 0; c < n_chunks; ++c) {
         const float4 b = partial[static_cast<size_t>(c) * n_pixels + i];
         a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;

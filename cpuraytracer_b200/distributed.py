@@ -33,12 +33,14 @@ def reduce_hdr(hdr_tensor, dst: int = 0, group=None):
 
 class ShardedAccumulator:
     """The multi-call protocol of a sharded render, independent of who renders (CUDA library, or the oracle in the gloo
-    tests): rank 0's buffer is the job's running sum (m_backbufferHdr); before each call every other rank zeroes its
-    buffer so the reduce adds only this call's frames to rank 0."""
+    tests): rank 0's buffer is the job's running sum (m_backbufferHdr); every other rank's buffer holds only the current
+    call's share, so the reduce adds only this call's frames to rank 0.  `render_into(first, n, overwrite)`: with
+    overwrite=True the renderer STARTS the sum (RT_FLAG_OVERWRITE: no clear, no read of the old content); a renderer that
+    cannot overwrite gets a zeroed buffer instead (overwrite_capable=False)."""
 
-    def __init__(self, hdr, render_into: Callable[[int, int], None], group=None):
+    def __init__(self, hdr, render_into: Callable[..., None], group=None, overwrite_capable: bool = False):
         import torch.distributed as dist
-        self.hdr, self.render_into, self.group = hdr, render_into, group
+        self.hdr, self.render_into, self.group, self.overwrite_capable = hdr, render_into, group, overwrite_capable
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.sample_count = 0
@@ -50,10 +52,14 @@ class ShardedAccumulator:
     def render(self, spp: int, first_sample: Optional[int] = None, reduce: bool = True):
         first = self.sample_count + 1 if first_sample is None else first_sample
         my_first, my_spp = shard_samples(first, spp, self.rank, self.world)
-        if reduce and self.rank != 0 and self.world > 1:
+        fresh = reduce and self.rank != 0 and self.world > 1
+        if fresh and not (self.overwrite_capable and my_spp > 0):
             self.hdr.zero_()
         if my_spp > 0:
-            self.render_into(my_first, my_spp)
+            if self.overwrite_capable:
+                self.render_into(my_first, my_spp, fresh)
+            else:
+                self.render_into(my_first, my_spp)
         if reduce:
             reduce_hdr(self.hdr, 0, self.group)
         self.sample_count += spp
@@ -76,8 +82,17 @@ class ShardedRenderer:
         self.renderer.bind_external_hdr(self.hdr.data_ptr())
         self.width, self.height = width, height
         self._depth, self._flags = 50, 0
-        self._acc = ShardedAccumulator(self.hdr, lambda first, n: self.renderer.render(n, self._depth, self._flags, first_sample=first), group)
+        self._acc = ShardedAccumulator(self.hdr, self._render_into, group, overwrite_capable=True)
         self.rank, self.world = self._acc.rank, self._acc.world
+
+    def _render_into(self, first: int, n: int, overwrite: bool) -> None:
+        from ._lib import RT_FLAG_DEBUG_ONE_KERNEL, RT_FLAG_OVERWRITE, RT_FLAG_WAVEFRONT
+        flags = self._flags
+        if overwrite and (flags & (RT_FLAG_WAVEFRONT | RT_FLAG_DEBUG_ONE_KERNEL)):
+            self.hdr.zero_()                                  # those schedules only add to the running sum
+        elif overwrite:
+            flags |= RT_FLAG_OVERWRITE
+        self.renderer.render(n, self._depth, flags, first_sample=first)
 
     @property
     def sample_count(self) -> int:

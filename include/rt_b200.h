@@ -69,8 +69,16 @@ enum { RT_FLAG_JITTER_OFF = 1u,   /* jitterOffset = 0 (spheres-app.cpp:140)     
  * instance (m_reflectionProbabilitySampleIndex / m_sampleIndex, material.h:34,50-51,67; material.cpp:29,44,82,151) -- instead
  * of the stateless counter RNG.  The indices are shared by all paths (device atomics), start at 0 in rt_set_scene and persist
  * across rt_render calls, as the reference's members do; like the reference, the result is reproducible only when paths run
- * one after another (1x1 framebuffer), and statistically equivalent otherwise.  Brute-force megakernel only. */
+ * one after another (1x1 framebuffer), and statistically equivalent otherwise.  Works with the brute-force query and with
+ * RT_FLAG_ACCEL, with one light or several (lights 1.. re-walk the batch's paths with the indices rewound, so every light
+ * sees the numbers light 0 saw -- the reference draws once per vertex and loops over its lights there, material.cpp:4-13). */
 enum { RT_FLAG_HALTON = 16u };
+/* RT_FLAG_OVERWRITE (32u): the call STARTS the running sum instead of adding to it -- the framebuffer's previous content is not
+ * read (saves the clear; used by ranks >= 1 of a sharded render, whose buffers hold only the current call's share). */
+enum { RT_FLAG_OVERWRITE = 32u };
+/* RT_FLAG_DEBUG_ONE_KERNEL (0x200u): the round-1 schedule -- primary rays traced inside the path megakernel instead of by the
+ * first-hit stage.  Same arithmetic per path; kept so that the choice of schedule stays a measurement (bench.py, profiles/). */
+enum { RT_FLAG_DEBUG_ONE_KERNEL = 0x200u };
 
 typedef struct rt_stats {
     uint64_t paths;            /* path samples traced since the last rt_stats_reset            */
@@ -133,7 +141,10 @@ RT_API int  rt_camera_basis_of(const rt_camera_params* cam, rt_camera_basis* out
 RT_API int  rt_set_exposure(rt_context* ctx, float stops);                   /* m_exposure, default -15: spheres-app.cpp:48 */
 RT_API int  rt_set_seed(rt_context* ctx, uint32_t seed);                     /* counter-RNG stream selector, default 0 */
 RT_API int  rt_sampler_reset(rt_context* ctx);                                /* RT_FLAG_HALTON: set every material's Halton indices back to 0 */
-RT_API int  rt_set_chunk_spp(rt_context* ctx, int chunk_spp);                /* 0 = auto; samples per work item (load balance) */
+RT_API int  rt_set_chunk_spp(rt_context* ctx, int chunk_spp);                /* 0 = auto; samples per work item (load balance); rounded up to a multiple of 8 */
+/* RT_FLAG_ACCEL: finest group size rt_set_scene may choose for the box hierarchy: 8, 16 or 32 slots per group (0 = default 8).
+ * Takes effect at the next rt_set_scene.  A tuning knob; every size returns the same bits. */
+RT_API int  rt_set_accel_group_slots(rt_context* ctx, int slots);
 /* InitBuffers (app.cpp:112-119): allocate W*H float4 running-sum + BGRA8 buffers, zero-filled. */
 RT_API int  rt_framebuffer_resize(rt_context* ctx, int width, int height);
 RT_API int  rt_framebuffer_clear(rt_context* ctx);
@@ -170,6 +181,8 @@ typedef struct rt_accel_image_info {
 } rt_accel_image_info;
 /* Fills `info`; copies the image into buf when buf != NULL (capacity >= info->bytes).  RT_ERR_UNSUPPORTED when the scene has no hierarchy. */
 RT_API int  rt_scene_accel_image(const rt_scene* scene, void* buf, size_t capacity, rt_accel_image_info* info);
+/* Same with the finest group size to try (8, 16 or 32 slots; 0 = default), as rt_set_accel_group_slots sets it for a context. */
+RT_API int  rt_scene_accel_image_slots(const rt_scene* scene, int min_group_slots, void* buf, size_t capacity, rt_accel_image_info* info);
 
 /* ---- interop / instrumentation ---- */
 RT_API void* rt_hdr_device_ptr(rt_context* ctx);                   /* float4[W*H] in HBM (e.g. for an NCCL reduce) */

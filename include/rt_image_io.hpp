@@ -131,8 +131,13 @@ inline void read_exr_sum(const std::string& path, std::vector<float>& hdr_sum, i
         if (name.empty()) break;
         const std::string type = cstr();
         const int32_t size = i32();
+        if (size < 0) throw std::runtime_error(path + ": negative attribute size");
         need(static_cast<size_t>(size));
         const size_t v = p;
+        auto at_least = [&](int32_t n) { if (size < n) throw std::runtime_error(path + ": attribute '" + name + "' is shorter than its type"); };
+        if (name == "dataWindow") at_least(16);
+        else if (name == "compression" || name == "lineOrder") at_least(1);
+        else if (name == "rtSampleCount") at_least(4);
         if (name == "dataWindow") { int32_t q[4]; std::memcpy(q, &b[v], 16); if (q[0] != 0 || q[1] != 0) throw std::runtime_error(path + ": dataWindow origin must be 0,0"); w = q[2] + 1; h = q[3] + 1; }
         else if (name == "compression") ok_comp = b[v] == 0;
         else if (name == "lineOrder") ok_order = b[v] == 0;

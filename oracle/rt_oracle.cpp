@@ -436,7 +436,12 @@ static inline bool scatter_with(const World& w, const Ray& r, const Hit& h, cons
     if (m.kind == ORC_MAT_METAL) {
         const float ndv = dot3(neg(r.d), h.n);
         if (!(ndv > 0.f)) return false;                                   /* :74 */
-        /* :81-85 compares 4 lanes; lane w of the reflectance is alpha == 1 > rand, so it always reflects. */
+        /* :77-85: reflectance = f0 + (1 - f0) (1 - n.v)^5 on all four lanes of the texture colour; reflect when ANY lane
+         * exceeds the random number.  Lane w is the texture's alpha: 1 in every scene the reference builds (then that lane is
+         * exactly 1 > rand: always reflects), but any alpha is representable. */
+        float c4[4]; texture_eval(w.sc->textures[m.texture], h.u, h.v, c4);
+        const float nv = saturate(ndv);
+        if (!(schlick(c4[0], nv) > rnd.xi || schlick(c4[1], nv) > rnd.xi || schlick(c4[2], nv) > rnd.xi || schlick(c4[3], nv) > rnd.xi)) return false;
         atten = texture_rgb(w, m.texture, h.u, h.v);                      /* :87 */
         out = Ray{h.pos, normalize3(reflect3(r.d, h.n))};                 /* :89-90 */
         return true;

@@ -107,8 +107,7 @@ def _rays(rng, centres, radii, n_rays):
 
 
 @pytest.mark.parametrize("which", ["d488", "random600", "s4096"])
-def test_filters_never_drop_what_the_exact_test_accepts(rt, monkeypatch, which):
-    monkeypatch.delenv("RT_ACCEL_GSHIFT", raising=False)
+def test_filters_never_drop_what_the_exact_test_accepts(rt, which):
     scene = _random_flat_scene(rt, 21, 600, ground=True) if which == "random600" else rt.scenes.NAMED[which]()
     info, img = scene.accel_image()
     cx, cy, cz, w, R, I, box, top = _accel_sections(info, img)

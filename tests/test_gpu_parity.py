@@ -377,9 +377,9 @@ def test_accel_equals_brute_force_on_random_scenes(gpu, seed, n, spread, extent,
 
 
 @pytest.mark.parametrize("name,n_random", [("d488", 0), ("s4096", 0), ("random", 900)])
-def test_accel_group_sizes_equal_brute_force(gpu, scene_factory, monkeypatch, name, n_random):
-    """build_accel picks the finest of 8 / 16 / 32 slots per group that fits the 32 x 8 fan-out; RT_ACCEL_GSHIFT forces a
-    coarser one.  Every size (a different kernel instantiation and image layout each) must reproduce brute force bit for bit,
+def test_accel_group_sizes_equal_brute_force(gpu, scene_factory, name, n_random):
+    """build_accel picks the finest of 8 / 16 / 32 slots per group that fits the 32 x 8 fan-out; rt_set_accel_group_slots forces
+    a coarser one.  Every size (a different kernel instantiation and image layout each) must reproduce brute force bit for bit,
     and a finer size must evaluate fewer sphere tests."""
     rt = gpu
     w, h = 160, 90
@@ -389,7 +389,6 @@ def test_accel_group_sizes_equal_brute_force(gpu, scene_factory, monkeypatch, na
     else:
         scene, _ = scene_factory(name)
         cam = rt.scenes.default_camera(aspect=w / h)
-    monkeypatch.delenv("RT_ACCEL_GSHIFT", raising=False)
     r = _renderer(rt, scene, cam, w, h)
     r.reset_stats(); r.render(3, 50, 0)
     ref, sref = r.read_hdr_sum(), r.stats()
@@ -397,8 +396,9 @@ def test_accel_group_sizes_equal_brute_force(gpu, scene_factory, monkeypatch, na
     r.close()
     tests = {}
     for g in (3, 4, 5):
-        monkeypatch.setenv("RT_ACCEL_GSHIFT", str(g))
-        r = _renderer(rt, scene, cam, w, h)              # rt_set_scene reads the override
+        r = _renderer(rt, scene, cam, w, h)
+        r.set_accel_group_slots(1 << g)                  # takes effect at the next rt_set_scene
+        r.set_scene(scene)
         r.reset_stats(); r.render(3, 50, rt.RT_FLAG_ACCEL)
         b, sb = r.read_hdr_sum(), r.stats()
         assert np.array_equal(ref, b, equal_nan=True), g
@@ -432,28 +432,36 @@ def test_accel_empty_scene_and_limits(gpu):
 
 
 # ---------------------------------------------------------------- RT_FLAG_HALTON: the reference's own sampler on the GPU (F4)
+@pytest.mark.parametrize("query,n_lights", [("brute", 1), ("accel", 1), ("brute", 3), ("accel", 3)])
 @pytest.mark.parametrize("look", [(0.0, 1.0, 0.0), (4.0, 1.0, 0.0), (-4.0, 0.6, 0.3), (2.0, 0.0, 1.0), (6.0, 0.2, -1.2)])
-def test_halton_sampler_sequential_paths_match_oracle(gpu, orc, scene_factory, look):
+def test_halton_sampler_sequential_paths_match_oracle(gpu, orc, look, query, n_lights):
     """With a 1x1 framebuffer and one work item the GPU traces its paths one after another, which is the only schedule under
     which the reference's shared per-material Halton indices (material.h:34,50-51,67) are reproducible: it must then follow
-    the oracle's single-threaded reference-sampler run path for path, across render calls (the indices persist)."""
+    the oracle's single-threaded reference-sampler run path for path, across render calls (the indices persist) -- with the
+    brute-force query and behind the box hierarchy (the reference's own combination: its sampler behind its BVH,
+    material.cpp:29,44,82,151 with ray-tracing.cpp:174-214), with one light and with several (material.cpp:4-13)."""
     rt = gpu
-    scene, osc = scene_factory("d488")
+    flags = rt.RT_FLAG_HALTON | (rt.RT_FLAG_ACCEL if query == "accel" else 0)
+    scene = rt.scenes.scene_d488()
+    if n_lights > 1:
+        scene.add_light(rt.DirectionalLight((-1.0, 0.6, 0.2), rt.XMCOLOR(0.3, 0.5, 1.0), 25000.0))
+        scene.add_light(rt.DirectionalLight((0.1, 1.0, -0.9), rt.XMCOLOR(1.0, 0.4, 0.3), 15000.0))
+    osc = orc.Scene.from_flat(scene.export())
     cam = rt.Camera((12.0, 2.0, -2.5), look, 4.0, 1.0, 12.0, 0.4)
     r = _renderer(rt, scene, cam, 1, 1)
     r.set_chunk_spp(1 << 20)
     r.reset_stats()
-    r.render(40, 50, rt.RT_FLAG_HALTON)
-    r.render(24, 50, rt.RT_FLAG_HALTON)
+    r.render(40, 50, flags)
+    r.render(24, 50, flags)
     g, st = r.read_hdr_sum(), r.stats()
     o, ost = orc.render(osc, orc_camera(orc, cam), orc.config(1, 1, spp=64, rng_mode=orc.RNG_HALTON, threads=1))
     assert (st.paths, st.closest_rays, st.shadow_rays) == (ost.paths, ost.closest_rays, ost.shadow_rays)
     assert _close(g, o) < RTOL
     # and it is a different sample set from the counter RNG (the flag does something)
-    r.clear(); r.render(64, 50, 0)
+    r.clear(); r.render(64, 50, flags & ~rt.RT_FLAG_HALTON)
     assert not np.array_equal(r.read_hdr_sum(), g)
     # reset_sampler == fresh scene
-    r.clear(); r.reset_sampler(); r.render(64, 50, rt.RT_FLAG_HALTON)
+    r.clear(); r.reset_sampler(); r.render(64, 50, flags)
     assert _close(r.read_hdr_sum(), o) < RTOL
 
 
@@ -479,7 +487,7 @@ def test_halton_sampler_converges_to_reference_sampler(gpu, orc, scene_factory):
     assert mean_rel_err(g, ref[..., :3] / spp) < 5e-3
     assert got < 1.5 * floor + 1e-2
     with pytest.raises(rt.RtError):
-        r.render(1, 50, rt.RT_FLAG_HALTON | rt.RT_FLAG_ACCEL)
+        r.render(1, 50, rt.RT_FLAG_HALTON | rt.RT_FLAG_WAVEFRONT)
 
 
 # ---------------------------------------------------------------- several lights (Material::Shade loops over m_lights, material.cpp:4-13)
@@ -509,7 +517,7 @@ def test_several_lights_match_oracle(gpu, orc, flags_name):
     r1.render(spp, 50, flags)
     assert not np.allclose(r1.read_hdr_sum()[..., :3], g[..., :3], rtol=1e-3)
     with pytest.raises(rt.RtError):
-        r.render(1, 50, rt.RT_FLAG_HALTON)
+        r.render(1, 50, rt.RT_FLAG_WAVEFRONT)
 
 
 # ---------------------------------------------------------------- converged images vs the committed reference-build goldens

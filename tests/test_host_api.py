@@ -207,10 +207,9 @@ def _random_flat_scene(rt, seed, n, ground):
 
 
 @pytest.mark.parametrize("which,expect_slots", [("d488", 8), ("s4096", 16), ("random600", 8), ("random6000", 32)])
-def test_accel_image_invariants(rt, monkeypatch, which, expect_slots):
+def test_accel_image_invariants(rt, which, expect_slots):
     """What makes RT_FLAG_ACCEL equal to brute force is decided on the host: every sphere sits in exactly one slot with the
     same cull constants as the brute-force arrays, and every box contains the spheres below it, rounded outward."""
-    monkeypatch.delenv("RT_ACCEL_GSHIFT", raising=False)
     if which.startswith("random"):
         scene = _random_flat_scene(rt, 5, int(which[6:]), ground=True)
     else:
@@ -262,15 +261,15 @@ def test_accel_image_invariants(rt, monkeypatch, which, expect_slots):
         assert info.c_max >= np.abs(np.concatenate([centres[sm] - radii[sm, None], centres[sm] + radii[sm, None]])).max()
 
 
-def test_accel_image_group_size_override_and_limits(rt, monkeypatch):
+def test_accel_image_group_size_override_and_limits(rt):
     scene = rt.scenes.NAMED["d488"]()
     slots = {}
     for g in (3, 4, 5):
-        monkeypatch.setenv("RT_ACCEL_GSHIFT", str(g))
-        info, _ = scene.accel_image()
+        info, _ = scene.accel_image(min_group_slots=1 << g)      # rt_scene_accel_image_slots (no environment variable is read)
         slots[g] = (info.group_slots, info.n_groups)
     assert slots == {3: (8, 61), 4: (16, 31), 5: (32, 16)}
-    monkeypatch.delenv("RT_ACCEL_GSHIFT")
+    with pytest.raises(rt.RtError):
+        scene.accel_image(min_group_slots=12)
     too_many = _random_flat_scene(rt, 9, 8300, ground=False)                          # > 8192 small spheres: no hierarchy
     with pytest.raises(rt.RtError) as e:
         too_many.accel_image()

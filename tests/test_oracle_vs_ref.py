@@ -175,7 +175,7 @@ def test_scatter_sequences_follow_the_atomic_counters(orc, ref, rt, scene_factor
                 sample += 1
             else:
                 # front-face test first (material.cpp:22,74): back-facing hits consume no sample
-                r0 = L.orc_scatter(C.byref(osc.c), sphere, orc.f3(*o[k]), orc.f3(*d[k]), 2.0, 0.0, 0.0, a, b, e)
+                r0 = L.orc_scatter(C.byref(osc.c), sphere, orc.f3(*o[k]), orc.f3(*d[k]), -1.0, 0.0, 0.0, a, b, e)   # xi = -1: every lane "reflects"
                 if r0 == 0:
                     assert sc[k] == 0
                     continue
@@ -217,6 +217,51 @@ def test_whole_render_bit_identical(orc, ref, rt, scene_factory, name, w, h, spp
                                                 integrator=orc.INTEGRATOR_RECURSIVE, math_mode=orc.MATH_REFERENCE))
         assert (ost.closest_rays, ost.shadow_rays) == (rst.closest_rays, rst.shadow_rays)
         assert np.array_equal(r, o)
+
+
+def test_metal_alpha_lane_any_of_four(orc, ref):
+    """Metal::Scatter reflects when ANY of the four lanes of f0 + (1 - f0)(1 - n.v)^5 exceeds the random number
+    (material.cpp:77-85); lane w is the texture's alpha.  With alpha < 1 and a dark reflectance the answer depends on the
+    angle and on the Halton coin: tier A (the reference's own Metal::Scatter) against tier B fed with the same coins."""
+    L = orc.load()
+    q = lambda x: L.orc_xmcolor_load(L.orc_xmcolor_quantize(x))  # noqa: E731  XMCOLOR round trip: k * (1/255.0f)
+    tex = np.zeros(1, orc.TEXTURE_DTYPE)
+    tex["kind"], tex["c0"], tex["c1"] = orc.MAT_OPAQUE * 0, [[q(0.1), q(0.15), q(0.05), q(0.3)]], [[q(0.1), q(0.15), q(0.05), q(0.3)]]
+    mat = np.zeros(1, orc.MATERIAL_DTYPE)
+    mat["kind"], mat["texture"], mat["smoothness"] = orc.MAT_METAL, 0, 0.0
+    sph = np.zeros(1, orc.SPHERE_DTYPE)
+    sph["cx"], sph["cy"], sph["cz"], sph["radius"], sph["material"] = 0.5, 1.0, -0.25, 1.0, 0
+    osc = orc.Scene(sph, mat, tex, np.zeros(0, orc.LIGHT_DTYPE), 1.0, 0)
+    rng = np.random.default_rng(17)
+    n = 400
+    c = np.array([0.5, 1.0, -0.25])
+    o = (c + rng.normal(size=(n, 3)) * 3.0).astype(np.float32)
+    tgt = c + rng.normal(size=(n, 3)) * 0.55
+    d = tgt - o
+    d = (d / np.linalg.norm(d, axis=1, keepdims=True)).astype(np.float32)
+    sc = np.zeros(n, np.int32)
+    at, oo, od = (np.zeros((n, 3), np.float32) for _ in range(3))
+    ref.ref_scatter_sequence(C.byref(osc.c), 0, n, o.ctypes.data, d.ctypes.data, sc.ctypes.data, at.ctypes.data, oo.ctypes.data, od.ctypes.data)
+    a, b, e = _f(3), _f(3), _f(3)
+    coin, outcomes = 0, {0: 0, 1: 0}
+    L.orc_set_math_mode(orc.MATH_REFERENCE)
+    try:
+        for k in range(n):
+            if sc[k] < 0:
+                continue
+            if L.orc_scatter(C.byref(osc.c), 0, orc.f3(*o[k]), orc.f3(*d[k]), -1.0, 0.0, 0.0, a, b, e) == 0:
+                assert sc[k] == 0                                 # back face: no coin consumed (material.cpp:74)
+                continue
+            xi = L.orc_halton(coin, 3)
+            coin += 1
+            r = L.orc_scatter(C.byref(osc.c), 0, orc.f3(*o[k]), orc.f3(*d[k]), xi, 0.0, 0.0, a, b, e)
+            assert r == sc[k], k
+            outcomes[r] += 1
+            if r:
+                assert _bits(a) == _bits(at[k]) and _bits(e) == _bits(od[k])
+    finally:
+        L.orc_set_math_mode(orc.MATH_PINNED)
+    assert outcomes[0] > 40 and outcomes[1] > 40                 # both answers really occur
 
 
 @pytest.mark.parametrize("flags,first", [(3, 1), (0, 1), (0, 9), (1, 4), (2, 1000)])
