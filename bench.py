@@ -52,6 +52,11 @@ def parse_args():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak (default, the driver's contract): every rank renders spp-step frames per step; strong: one step = the "
+                         "workload's whole config spp, split over the ranks")
+    ap.add_argument("--schedule", default="two-stage", choices=["two-stage", "one-kernel"], help="one-kernel = RT_FLAG_DEBUG_ONE_KERNEL (round-1 schedule)")
+    ap.add_argument("--no-extras", action="store_true", help="skip the short runs of the other BASELINE configs and the RMSE-vs-golden figures")
     ap.add_argument("--query", default="brute", choices=["brute", "accel"],
                     help="closest-hit / occlusion query of the timed steps: brute force over every sphere (north_star, default) or the "
                          "box hierarchy RT_FLAG_ACCEL (same bits); the default run also reports the other one under 'accel'")
@@ -212,6 +217,84 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------------ B200 arm
+def _fp32_roofline(tests, kern_s, world, traffic=None):
+    achieved = tests * FLOP_PER_TEST / kern_s / 1e12 / world            # per-GPU TFLOP/s of the render kernels
+    return {"bound": "fp32", "achieved": achieved, "peak": FP32_PEAK_MEASURED_TFLOPS, "unit": "TFLOP/s",
+            "frac": achieved / FP32_PEAK_MEASURED_TFLOPS, "traffic": traffic,
+            "note": "first-hit + path kernels: sphere tests x 17 flop / kernel time (cudaEvents on their stream); peak = measured "
+                    "FFMA-chain FP32 rate (MEASURED_PEAKS.json has no FP32 figure; nominal 148x128x2x1.965 GHz = 74.5)",
+            "sphere_tests_per_s": tests / kern_s / world}
+
+
+def short_config_runs(rt, local, flush, skip):
+    """Driver-observed figures for the BASELINE configs the timed region does not run (N = 1 only): 1 warm-up + 2 timed steps each,
+    brute force and RT_FLAG_ACCEL, CUDA events on the launch stream, L2 flushed between steps.  Short steps: seconds in total."""
+    import torch
+    out = {}
+    for wl, spp_b, spp_a in (("c1", 128, 256), ("c2", 128, 256), ("c3", 64, 128), ("c4", 32, 64), ("c5", 8, 32)):
+        if wl == skip:
+            continue
+        scene_name, w, h, depth, cfg_spp, desc = WORKLOADS[wl]
+        r = rt.Renderer(device=local, width=w, height=h, stream=torch.cuda.current_stream(local).cuda_stream)
+        r.set_scene(rt.scenes.NAMED[scene_name]())
+        r.set_camera(rt.scenes.default_camera(aspect=w / h))
+        entry = {"workload": desc, "width": w, "height": h, "max_depth": depth}
+        for name, flags, spp in (("brute", 0, spp_b), ("accel", rt.RT_FLAG_ACCEL, spp_a)):
+            r.render(spp, depth, flags, first_sample=1)
+            torch.cuda.synchronize()
+            r.clear(); r.reset_stats()
+            ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(2)]
+            for i in range(2):
+                flush.fill_(i)
+                ev[i][0].record()
+                r.render(spp, depth, flags, first_sample=1 + i * spp)
+                ev[i][1].record()
+            torch.cuda.synchronize()
+            ms = sum(a.elapsed_time(b) for a, b in ev)
+            st = r.stats()
+            assert st.paths == 2 * spp * w * h
+            entry[name] = {"value": st.paths / (ms * 1e-3), "unit": "path samples/s", "spp_per_step": spp, "steps": 2, "ms_per_step": ms / 2,
+                           "rays_per_path": (st.closest_rays + st.shadow_rays) / st.paths,
+                           "roofline_frac": st.sphere_tests * FLOP_PER_TEST / (st.render_ms * 1e-3) / 1e12 / FP32_PEAK_MEASURED_TFLOPS}
+        r.close()
+        out[wl] = entry
+    return out
+
+
+def rmse_vs_golden(rt, local):
+    """BASELINE.json's metric names "RMSE vs CPU ref": per config the GPU's converged linear radiance against the committed golden
+    of the reference's own renderer (tests/golden/golden_converged.npz: oracle/_ref at 65,536 spp, 240x135), same spp on the GPU.
+    Bars (north_star): per-pixel relRMSE < 1e-2, image-mean relative error < 0.5 %."""
+    import numpy as np
+    import torch
+    path = os.path.join(ROOT, "tests", "golden", "golden_converged.npz")
+    if not os.path.exists(path):
+        return None
+    gold = np.load(path)
+    if "spp" not in gold.files:
+        return None
+    spp = int(gold["spp"])
+    out = {"golden": "oracle/_ref (the reference's own sources) at %d spp, 240x135; tests/golden/make_golden_converged.py" % spp,
+           "bars": {"rel_rmse": 1e-2, "mean_rel_err": 5e-3}}
+    for key, scene_name, depth in (("c2", "d488", 0), ("c3", "d488", 50), ("c5", "s4096", 50)):
+        if key + "_mean" not in gold.files:
+            continue
+        ref = gold[key + "_mean"].astype(np.float64) * 1024.0
+        h, w = ref.shape[:2]
+        r = rt.Renderer(device=local, width=w, height=h, stream=torch.cuda.current_stream(local).cuda_stream)
+        r.set_scene(rt.scenes.NAMED[scene_name]())
+        r.set_camera(rt.scenes.default_camera(aspect=w / h))
+        r.render(spp, depth, rt.RT_FLAG_ACCEL)              # same bits as brute force (tests), several times faster on s4096
+        g = r.read_hdr_sum()
+        r.close()
+        mean = g[..., :3].astype(np.float64) / spp * 2.0 ** 15
+        rel = float(np.sqrt(np.mean(((mean - ref) / (ref + 1e-3 * ref.mean())) ** 2)))
+        merr = float(abs(mean.mean() - ref.mean()) / ref.mean())
+        out[key] = {"rel_rmse": rel, "mean_rel_err": merr, "golden_noise_estimate": float(gold[key + "_floor"]), "spp": spp, "scale": f"{w}x{h}",
+                    "pass": bool(rel < 1e-2 and merr < 5e-3)}
+    return out
+
+
 def run_b200(args):
     import numpy as np
     import torch
@@ -232,7 +315,10 @@ def run_b200(args):
         dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
 
     scene_name, w, h, depth, cfg_spp, desc = WORKLOADS[args.workload]
+    strong = args.scaling == "strong"
+    # weak: every rank renders spp_step frames per step; strong: one step = the config's whole spp, split over the ranks
     spp_step = args.spp_step or (32 if args.workload == "c5" else 256)
+    job_spp = cfg_spp if strong else world * spp_step        # frames of ONE step, all ranks together
     n_pix = w * h
     scene = rt.scenes.NAMED[scene_name]()
     flat = scene.export()
@@ -248,11 +334,26 @@ def run_b200(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    step_flags = rt.RT_FLAG_ACCEL if args.query == "accel" else 0
+    base_flags = {"brute": 0, "accel": rt.RT_FLAG_ACCEL}[args.query] | (rt.RT_FLAG_DEBUG_ONE_KERNEL if args.schedule == "one-kernel" else 0)
 
     def step(i, flags=None):
-        # global frame range of step i: [1 + i*world*spp_step, ...); each rank takes its disjoint share
-        sr.render(world * spp_step, depth, step_flags if flags is None else flags, first_sample=1 + i * world * spp_step, reduce=True)
+        # global frame range of step i: [1 + i*job_spp, ...); each rank takes its disjoint share
+        sr.render(job_spp, depth, base_flags if flags is None else flags, first_sample=1 + i * job_spp, reduce=True)
+
+    def timed(flags, steps):
+        """steps x step() with CUDA events on the launching stream, L2 flushed before each; returns max-over-ranks seconds."""
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        barrier()
+        for i in range(steps):
+            flush.fill_(i & 0xFF)
+            ev[i][0].record()
+            step(i, flags)
+            ev[i][1].record()
+        barrier()
+        ms = torch.tensor([sum(a.elapsed_time(b) for a, b in ev)], dtype=torch.float64, device=f"cuda:{local}")
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item()) * 1e-3
 
     # ---- warm-up ----
     for i in range(args.warmup):
@@ -261,38 +362,26 @@ def run_b200(args):
     sr.clear()
     r.reset_stats()
 
-    # ---- timed region: exactly K steps, CUDA events on the launching stream, L2 flushed between steps ----
+    # ---- timed region: exactly K steps ----
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    barrier()
     t_wall0 = time.perf_counter()
-    for i in range(args.steps):
-        flush.fill_(i & 0xFF)
-        ev[i][0].record()
-        step(i)
-        ev[i][1].record()
-    barrier()
+    total_s = timed(None, args.steps)
     t_wall = time.perf_counter() - t_wall0
     clocks = sampler.stop() if rank == 0 else None
-    ms_steps = [a.elapsed_time(b) for a, b in ev]
-    total_ms = torch.tensor([sum(ms_steps)], dtype=torch.float64, device=f"cuda:{local}")
     st = r.stats()
     counts = torch.tensor([st.paths, st.closest_rays, st.shadow_rays, st.sphere_tests, st.launches], dtype=torch.float64, device=f"cuda:{local}")
     kern_ms = torch.tensor([st.render_ms], dtype=torch.float64, device=f"cuda:{local}")
     if world > 1:
-        dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
         dist.all_reduce(kern_ms, op=dist.ReduceOp.MAX)
         dist.all_reduce(counts, op=dist.ReduceOp.SUM)
-    total_s = float(total_ms.item()) * 1e-3
-    paths = world * spp_step * n_pix * args.steps
+    paths = job_spp * n_pix * args.steps
     assert int(counts[0].item()) == paths, (int(counts[0].item()), paths)
     value = paths / total_s
-    # sanity: rank 0 holds the whole job's sum -> every pixel accumulated K * world * spp_step samples
-    if rank == 0:
-        wsum = float(sr.hdr[..., 3].double().mean().item())
-        assert abs(wsum - args.steps * world * spp_step) < 1e-3 * wsum, wsum
+    if rank == 0:      # rank 0 holds the whole job's sum -> every pixel accumulated K * job_spp samples, exactly
+        wch = sr.hdr[..., 3]
+        assert float(wch.min().item()) == float(wch.max().item()) == float(args.steps * job_spp), (float(wch.min().item()), float(wch.max().item()))
 
     # ---- K5, the only HBM-bound kernel of the path (north_star: "HBM GB/s is reported only for the accumulation pass"):
     #      resolve = 16 B read + 4 B write per pixel, L2 flushed before every launch, CUDA events inside rt_resolve_ldr ----
@@ -302,7 +391,7 @@ def run_b200(args):
         n_res = 10
         for i in range(n_res):
             flush.fill_(i & 0xFF)
-            r.resolve_ldr(sample_count=args.steps * world * spp_step, copy=False)
+            r.resolve_ldr(sample_count=args.steps * job_spp, copy=False)
         rs = r.stats()
         res_s = rs.resolve_ms * 1e-3 / n_res
         hbm_peak = 6550.7
@@ -315,26 +404,19 @@ def run_b200(args):
                         "note": "peak = MEASURED_PEAKS.json hbm_gbs (driver-measured copy bandwidth)"}
         r.reset_stats()
 
-    # ---- the other query mode on the same steps (informative; same bits, see tests/test_gpu_parity.py) ----
-    other = None
-    if args.query == "brute":
-        for i in range(2):
-            step(i, rt.RT_FLAG_ACCEL)
-        barrier()
-        sr.clear()
-        oev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-        for i in range(args.steps):
-            flush.fill_(i & 0xFF)
-            oev[i][0].record()
-            step(i, rt.RT_FLAG_ACCEL)
-            oev[i][1].record()
-        barrier()
-        oms = torch.tensor([sum(a.elapsed_time(b) for a, b in oev)], dtype=torch.float64, device=f"cuda:{local}")
-        if world > 1:
-            dist.all_reduce(oms, op=dist.ReduceOp.MAX)
-        other = {"query": "RT_FLAG_ACCEL box hierarchy (bit-identical results)", "value": paths / (float(oms.item()) * 1e-3),
-                 "unit": "path samples/s", "ms_per_step": float(oms.item()) / args.steps}
-        sr.clear()
+    # ---- the same steps with the other query mode and with the round-1 schedule (informative; same bits, see tests) ----
+    others = {}
+    if args.query == "brute" and args.schedule == "two-stage" and not strong:
+        for name, flags in (("accel", rt.RT_FLAG_ACCEL), ("one_kernel_schedule", rt.RT_FLAG_DEBUG_ONE_KERNEL)):
+            k = min(args.steps, 3)
+            step(0, flags)
+            barrier()
+            sr.clear()
+            s_ = timed(flags, k)
+            others[name] = {"value": job_spp * n_pix * k / s_, "unit": "path samples/s", "ms_per_step": 1e3 * s_ / k, "steps": k}
+            sr.clear()
+        others["accel"]["query"] = "RT_FLAG_ACCEL box hierarchy (bit-identical results)"
+        others["one_kernel_schedule"]["note"] = "RT_FLAG_DEBUG_ONE_KERNEL: primary rays inside the path megakernel (round-1 schedule), brute force"
 
     # ---- end to end through the public API with HOST buffers: scene arrays -> rt_scene_import/rt_set_scene (H2D),
     #      render (+ reduce), running-sum buffer -> pinned host memory (D2H) ----
@@ -359,38 +441,42 @@ def run_b200(args):
     e2e_value = paths / float(e2e_s.item())
 
     parity_n = parity_across_gpus(rt, ShardedRenderer, scene, depth, world, rank, local) if world > 1 else None
+    extra_configs = short_config_runs(rt, local, flush, args.workload) if (world == 1 and rank == 0 and not args.no_extras) else None
+    rmse = rmse_vs_golden(rt, local) if (rank == 0 and not args.no_extras) else None
 
     if rank == 0:
         kern_s = float(kern_ms.item()) * 1e-3
         tests = float(counts[3].item())
-        achieved = tests * FLOP_PER_TEST / kern_s / 1e12 / world            # per-GPU TFLOP/s of the render kernel
+        roof = _fp32_roofline(tests, kern_s, world, _ncu_traffic(args.workload, args.query))
+        roof["kernel_ms_per_step"] = 1e3 * kern_s / args.steps
         line = {
             "metric": "path samples/s", "value": value, "unit": "path samples/s", "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": 1e3 * total_s / args.steps, "higher_is_better": True, "scaling": "weak",
+            "warmup": args.warmup, "ms_per_step": 1e3 * total_s / args.steps, "higher_is_better": True, "scaling": args.scaling,
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": f"{args.workload} {desc}", "scene": scene_name, "n_spheres": int(len(flat.spheres)), "width": w,
-                       "height": h, "max_depth": depth, "spp_per_step_per_gpu": spp_step, "config_spp": cfg_spp,
+                       "height": h, "max_depth": depth, "spp_per_step_per_gpu": job_spp / world, "config_spp": cfg_spp,
                        "partition": "disjoint sample ranges per GPU + ncclReduce(sum) to rank 0" if world > 1 else "single GPU",
                        "query": "RT_FLAG_ACCEL box hierarchy in front of the cull + exact tests" if args.query == "accel" else "brute force over every sphere (north_star)",
+                       "schedule": "two-stage: first-hit kernel + path megakernel" if args.schedule == "two-stage" else "one kernel (round-1 schedule)",
                        "l2": "flushed between timed steps (256 MiB fill); scene lives in shared memory"},
             "rays_per_s": (float(counts[1].item()) + float(counts[2].item())) / total_s,
             "rays_per_path": (float(counts[1].item()) + float(counts[2].item())) / paths,
             "gpu_launches": int(counts[4].item()),
             "e2e": {"value": e2e_value, "unit": "path samples/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
-            "roofline": {"bound": "fp32", "achieved": achieved, "peak": FP32_PEAK_MEASURED_TFLOPS, "unit": "TFLOP/s",
-                         "frac": achieved / FP32_PEAK_MEASURED_TFLOPS, "traffic": _ncu_traffic(args.workload, args.query),
-                         "note": "rt_render_kernel: sphere tests x 17 flop / kernel time (cudaEvents on its stream); peak = measured "
-                                 "FFMA-chain FP32 rate (MEASURED_PEAKS.json has no FP32 figure; nominal 148x128x2x1.965 GHz = 74.5)",
-                         "sphere_tests_per_s": tests / kern_s / world, "kernel_ms_per_step": 1e3 * kern_s / args.steps},
+            "roofline": roof,
             "clocks": clocks, "wall_s": t_wall,
         }
         if parity_n is not None:
             line["parity_n"] = parity_n
-        if other is not None:
-            other["speedup_vs_value"] = other["value"] / value
-            line["accel"] = other
+        for k_, v_ in others.items():
+            v_["speedup_vs_value"] = v_["value"] / value
+            line[k_] = v_
         if accumulation is not None:
             line["accumulation"] = accumulation
+        if extra_configs:
+            line["configs"] = extra_configs
+        if rmse:
+            line["rmse"] = rmse
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(args.workload, args.cpu_seconds)
         _emit(line)

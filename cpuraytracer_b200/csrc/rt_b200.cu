@@ -910,8 +910,9 @@ static int render_two_stage(rt_context* c, rt::RenderParams& p, int spp, int max
     const int grid = c->prop.multiProcessorCount * bps;
     const void* k_first = first_hit_kernel(mode, gshift);
     const void* k_path = path_kernel(mode, halton, gshift, direct);
-    // batch: as many frames as fit first-hit records of 512 MiB (2 B per pixel and frame), a multiple of 8, at most 4096
-    const size_t cap_bytes = 512ull << 20;
+    // batch: as many frames as fit first-hit records of max(256 MiB, two running-sum buffers) (2 B per pixel and frame), a
+    // multiple of 8, at most 4096: 64 frames at 1920x1080, 16 at 3840x2160 -- the records are the only per-batch allocation
+    const size_t cap_bytes = std::max<size_t>(256ull << 20, n_pix * 32);
     int batch = static_cast<int>(std::min<size_t>(4096, std::max<size_t>(8, (cap_bytes / (n_pix * 2)) & ~static_cast<size_t>(7))));
     batch = std::min(batch, (spp + 7) & ~7);
     const size_t hits_need = n_pix * static_cast<size_t>(batch) * sizeof(uint16_t);
@@ -927,10 +928,10 @@ static int render_two_stage(rt_context* c, rt::RenderParams& p, int spp, int max
         p = base;
         p.batch_s0 = s0; p.batch_n = std::min(batch, spp - s0); p.hit_stride = (p.batch_n + 7) & ~7;
         // work items of stage 2: (pixel, chunk of the batch).  One chunk keeps the reference's sequential per-pixel sum order and
-        // needs no partial buffers; small images are split so that every lane sees >= ~16 items (load balance at the tail).
+        // needs no partial buffers; small images are split so that every lane sees >= ~4 items (load balance at the tail).
         int chunk = c->chunk_spp > 0 ? ((c->chunk_spp + 7) & ~7) : 0;
         if (chunk <= 0) {
-            const u64 want = std::max<u64>(1, (16 * lanes + n_pix - 1) / n_pix);
+            const u64 want = std::max<u64>(1, (4 * lanes) / n_pix);          // one chunk from ~530k pixels up (1280x720 and larger)
             const int n_chunks = static_cast<int>(std::min<u64>(want, static_cast<u64>(p.hit_stride / 8)));
             chunk = (((p.batch_n + n_chunks - 1) / n_chunks) + 7) & ~7;
         }

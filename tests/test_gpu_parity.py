@@ -548,3 +548,112 @@ def test_converged_image_matches_reference_golden(gpu, key, name, depth):
     assert got < 1.5 * floor + 1e-2
     if floor < 2e-3:
         assert got < 1e-2                            # resolvable: the BASELINE bar itself
+
+
+# ---------------------------------------------------------------- round 2: schedule, overwrite, asynchrony, metal alpha
+@pytest.mark.parametrize("name,w,h,spp,depth,flags", [
+    ("d488", 320, 180, 8, 50, 0),
+    ("d488", 203, 117, 8, 50, 8),          # RT_FLAG_ACCEL, ragged size
+    ("small", 160, 90, 8, 0, 0),           # direct only: the shadow-only path kernel
+    ("s4096", 160, 90, 8, 3, 8),
+])
+def test_two_stage_schedule_equals_one_kernel(gpu, scene_factory, name, w, h, spp, depth, flags):
+    """The default schedule (first-hit kernel + path megakernel regenerating from the hit records) runs the same arithmetic per
+    path as the round-1 one-kernel megakernel; with one chunk per pixel the per-pixel sums are added in the same (sample)
+    order, so the running sums, the primary-hit buffers and every ray counter are identical."""
+    rt = gpu
+    scene, _ = scene_factory(name)
+    cam = rt.scenes.default_camera(aspect=w / h)
+    r = _renderer(rt, scene, cam, w, h)
+    r.set_chunk_spp(8)
+    r.reset_stats(); r.render(spp, depth, flags)
+    a, sa = r.read_hdr_sum(), r.stats()
+    r.clear(); r.reset_stats(); r.render(spp, depth, flags | rt.RT_FLAG_DEBUG_ONE_KERNEL)
+    b, sb = r.read_hdr_sum(), r.stats()
+    assert np.array_equal(a, b)
+    assert (sa.paths, sa.closest_rays, sa.shadow_rays, sa.sphere_tests) == (sb.paths, sb.closest_rays, sb.shadow_rays, sb.sphere_tests)
+
+
+def test_batches_and_chunks_change_only_the_summation_order(gpu, scene_factory):
+    """A call longer than one batch of first-hit records and a call split into chunks add the same samples."""
+    rt = gpu
+    scene, _ = scene_factory("small")
+    r = _renderer(rt, scene, rt.scenes.default_camera(aspect=16 / 9), 96, 54)
+    r.set_chunk_spp(1 << 20)
+    r.render(4200, 4)                      # batch cap is 4096 frames: 2 batches, sequential sums
+    a = r.read_hdr_sum()
+    r.clear(); r.set_chunk_spp(0)          # auto: a small image is split into chunks (partial buffers + combine)
+    r.render(4200, 4)
+    b = r.read_hdr_sum()
+    assert np.all(a[..., 3] == 4200) and np.all(b[..., 3] == 4200)
+    assert _close(b, a) < 1e-4
+    r.clear(); r.render(4096, 4); r.render(104, 4)
+    assert _close(r.read_hdr_sum(), a) < 1e-4
+
+
+def test_overwrite_flag_starts_the_running_sum(gpu, scene_factory):
+    rt = gpu
+    scene, _ = scene_factory("d488")
+    for w, h, spp in ((256, 144, 8), (64, 36, 256)):           # one chunk (direct store) and several chunks (combine)
+        r = _renderer(rt, scene, rt.scenes.default_camera(aspect=w / h), w, h)
+        r.render(spp, 50, 0, first_sample=5)
+        a = r.read_hdr_sum()
+        r.write_hdr_sum(np.full((h, w, 4), 7.0, np.float32), 1)    # garbage the overwrite must not read
+        r.render(spp, 50, rt.RT_FLAG_OVERWRITE, first_sample=5)
+        assert np.array_equal(a, r.read_hdr_sum())
+        r.render(spp, 50, 0, first_sample=5 + spp)                 # and the next call adds as usual
+        assert np.all(r.read_hdr_sum()[..., 3] == 2 * spp)
+        with pytest.raises(rt.RtError):
+            r.render(1, 50, rt.RT_FLAG_OVERWRITE | rt.RT_FLAG_DEBUG_ONE_KERNEL)
+        r.close()
+
+
+def test_render_call_is_asynchronous(gpu, scene_factory):
+    """rt_render only enqueues work on the context's stream (Halton tables are built on the device, no host copy, no
+    synchronisation): the call returns long before the kernels finish."""
+    import time
+    rt = gpu
+    scene, _ = scene_factory("d488")
+    r = _renderer(rt, scene, rt.scenes.default_camera(aspect=16 / 9), 1280, 720)
+    r.render(8, 50); r.synchronize()                       # warm-up: allocations, module load
+    t0 = time.perf_counter()
+    r.render(128, 50)
+    t_call = time.perf_counter() - t0
+    r.synchronize()
+    t_total = time.perf_counter() - t0
+    assert t_total > 0.03, t_total                         # ~70 ms of device work
+    assert t_call < 0.25 * t_total, (t_call, t_total)
+    assert np.all(r.read_hdr_sum()[..., 3] == 136)
+
+
+def test_metal_alpha_lane_matches_oracle(gpu, orc):
+    """Metal::Scatter reflects when any of the FOUR lanes of the Schlick reflectance exceeds the random number; lane w is the
+    texture's alpha (material.cpp:77-85).  With alpha < 1 and dark colours some metal hits end the path: the GPU must follow the
+    oracle path for path (tier B follows the reference's own Metal::Scatter: tests/test_oracle_vs_ref.py)."""
+    rt = gpu
+    scene = rt.Scene()
+    scene.add(rt.Sphere((0.0, -1000.0, 0.0), 1000.0, rt.DielectricOpaque(rt.CheckerTexture(rt.XMCOLOR(0.9, 0.9, 0.9), rt.XMCOLOR(0.2, 0.3, 0.1), 2500.0), 16.0)))
+    rng = np.random.default_rng(5)
+    for a in range(-4, 4):
+        for b in range(-4, 4):
+            col = rt.XMCOLOR(*(float(x) for x in rng.uniform(0.02, 0.3, 3)), float(rng.uniform(0.0, 0.6)))
+            scene.add(rt.Sphere((a + 0.5, 0.35, b + 0.5), 0.35, rt.Metal(rt.ConstTexture(col), 0.0)))
+    scene.add(rt.Sphere((0.0, 1.2, 0.0), 1.2, rt.Metal(rt.CheckerTexture(rt.XMCOLOR(0.1, 0.1, 0.1, 0.2), rt.XMCOLOR(0.7, 0.6, 0.5, 1.0), 8.0), 0.0)))
+    scene.set_sky(rt.Emissive(8000.0, rt.ConstTexture(rt.XMCOLOR(0.85, 0.91, 0.98, 1.0))))
+    scene.add_light(rt.DirectionalLight((1.0, 1.0, 1.0), rt.XMCOLOR(1.0, 0.97, 0.88, 1.0), 40000.0))
+    osc = orc.Scene.from_flat(scene.export())
+    w, h, spp = 160, 90, 4
+    cam = rt.scenes.default_camera(aspect=w / h)
+    o, ost = orc.render(osc, orc_camera(orc, cam), orc.config(w, h, spp=spp))
+    for flags in (0, rt.RT_FLAG_ACCEL, rt.RT_FLAG_DEBUG_ONE_KERNEL):
+        r = _renderer(rt, scene, cam, w, h)
+        r.reset_stats(); r.render(spp, 50, flags)
+        g, st = r.read_hdr_sum(), r.stats()
+        assert (st.paths, st.closest_rays, st.shadow_rays) == (ost.paths, ost.closest_rays, ost.shadow_rays), flags
+        assert _close(g, o) < RTOL
+        r.close()
+    # the alpha lane matters: the same scene with opaque alpha traces longer paths
+    flat = scene.export()
+    flat.textures["c0"][:, 3] = 1.0; flat.textures["c1"][:, 3] = 1.0
+    _, ost1 = orc.render(orc.Scene.from_flat(flat), orc_camera(orc, cam), orc.config(w, h, spp=spp))
+    assert ost1.closest_rays > ost.closest_rays

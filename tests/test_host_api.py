@@ -296,3 +296,62 @@ def test_bench_reference_arm_prints_the_contract_line():
     other = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2", "--steps", "1", "--warmup", "0"],
                            capture_output=True, text=True, timeout=600, env=dict(os.environ, RANK="1", WORLD_SIZE="2"))
     assert other.returncode == 0 and other.stdout.strip() == ""
+
+
+def test_frozen_scene_files_equal_the_recorder(rt, orc):
+    """oracle/scenes/*.rtsc (the CPU arm's input) are byte-identical to what the product's recorder exports for the named
+    scenes, and the oracle's own default camera equals the product's."""
+    for name in ("d488", "s4096", "small"):
+        flat = rt.scenes.NAMED[name]().export()
+        fz = orc.frozen_scene(name)
+        assert fz.spheres.tobytes() == flat.spheres.tobytes() and fz.materials.tobytes() == flat.materials.tobytes()
+        assert fz.textures.tobytes() == flat.textures.tobytes() and fz.lights.tobytes() == flat.lights.tobytes()
+        assert (fz.c.sky_luminance, fz.c.sky_texture) == (flat.sky_luminance, flat.sky_texture)
+    for aspect in (16 / 9, 1280 / 720, 4 / 3):
+        cam = rt.scenes.default_camera(aspect=aspect)
+        a = orc.default_camera_params(aspect)
+        b = orc.camera_params(cam.origin, cam.look_at, cam.vertical_fov, cam.aspect_ratio, cam.focal_length, cam.aperture)
+        assert bytes(a) == bytes(b)
+
+
+def test_cpu_arm_does_not_map_the_product_library():
+    """bench.py's CPU arm (cpu_baseline / --impl reference) takes its scene from the frozen files and runs oracle code only:
+    after a frame, no librt_b200 is mapped into the process and cpuraytracer_b200 was never imported."""
+    import subprocess
+    import sys
+    code = ("import sys; sys.path.insert(0, %r); import bench\n"
+            "bench.WORKLOADS['t'] = ('small', 64, 36, 50, 1, 'tiny')\n"
+            "arm = bench.CpuArm('t'); st = arm.frames(2); assert st.paths == 2 * 64 * 36\n"
+            "d = arm.describe(); assert d['counters'].startswith('per-thread') and d['kind'] in ('reference', 'port')\n"
+            "maps = open('/proc/self/maps').read()\n"
+            "assert 'librt_b200' not in maps, 'product library mapped'\n"
+            "assert not any(m.startswith('cpuraytracer_b200') for m in sys.modules), 'product package imported'\n"
+            "print('ok', d['kind'], 'libref' in maps)\n") % ROOT
+    out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0 and out.stdout.startswith("ok"), out.stderr[-2000:]
+
+
+def test_import_rejects_what_the_recorder_rejects(rt):
+    """rt_scene_import (scene files, Scene.from_flat) applies the recorder's checks: finite geometry, radius > 0, ior > 0,
+    known texture kinds, finite colours / tiling / luminance."""
+    base = rt.scenes.scene_small().export()
+    import copy
+
+    def broken(edit):
+        f = copy.deepcopy(base)
+        edit(f)
+        with pytest.raises(rt.RtError) as e:
+            rt.Scene.from_flat(f)
+        assert e.value.code == 1
+
+    glass = int(np.nonzero(base.materials["kind"] == 2)[0][0])
+    broken(lambda f: f.materials["ior"].__setitem__(glass, 0.0))
+    broken(lambda f: f.materials["ior"].__setitem__(glass, np.inf))
+    broken(lambda f: f.spheres["cx"].__setitem__(3, np.nan))
+    broken(lambda f: f.spheres["radius"].__setitem__(3, np.inf))
+    broken(lambda f: f.textures["kind"].__setitem__(0, 7))
+    broken(lambda f: f.textures["tiling"].__setitem__(0, np.nan))
+    broken(lambda f: f.textures["c0"].__setitem__((1, 2), np.inf))
+    broken(lambda f: f.lights["luminance"].__setitem__(0, np.nan))
+    broken(lambda f: f.lights["dir"].__setitem__(0, 0.0))
+    rt.Scene.from_flat(base)                                     # the unbroken scene still loads

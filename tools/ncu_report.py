@@ -65,8 +65,12 @@ def main():
                                        ("brute_cull_lists", r"^struct QueryResult"), ("exact_candidate", r"bool exact_candidate"),
                                        ("brute_cull_pair", r"^struct CullRay "), ("brute_query", r"QueryResult fused_query\(")])
             + ranges("rt_kernels.cuh", [("stage_scene", r"void stage_scene"), ("direct_light", r"V3 direct_unshadowed"), ("scatter", r"bool scatter\("),
-                                        ("halton_draw", r"void draw_halton"), ("work_items", r"bool item_to_pixel"), ("path_loop", r"void .*rt_render_kernel"),
-                                        ("other_kernels", r"void rt_combine_kernel")])
+                                        ("halton_draw", r"void draw_halton"), ("work_items", r"bool item_to_pixel"), ("one_kernel_path_loop", r"void .*rt_render_kernel"),
+                                        ("first_hit_kernel", r"void .*rt_first_hit_kernel"), ("path_setup", r"void .*rt_path_kernel"),
+                                        ("path_regeneration", r"// ---- regeneration: work items"), ("path_primary_vertex", r"// ---- K1 again for the regenerated"),
+                                        ("path_shade_glue", r"// ---- K4 at the vertex in hand"), ("path_query_call", r"fused closest-hit / shadow query ----\s*$"),
+                                        ("path_resolve", r"// ---- resolve the pass"), ("path_stats", r"primary rays were counted by stage 1"),
+                                        ("tables_kernel", r"Per-call Halton tables on the device"), ("other_kernels", r"^// hdr\[p\] = ")])
             + ["shf_funnel:sm_32_intrinsics:0-99999", "shfl_vote:sm_30_intrinsics:0-99999"])
     phases = sh(f"{sys.executable} {tools}/ncu_by_phase.py {full} " + " ".join(spec))
     open(out + "_by_phase.txt", "w").write(f"# {match[0]}, by phase (tools/ncu_report.py: ranges from anchors in the current sources)\n" + phases
