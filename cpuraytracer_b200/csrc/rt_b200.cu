@@ -927,17 +927,30 @@ static int render_two_stage(rt_context* c, rt::RenderParams& p, int spp, int max
     for (int s0 = 0; s0 < spp; s0 += batch) {
         p = base;
         p.batch_s0 = s0; p.batch_n = std::min(batch, spp - s0); p.hit_stride = (p.batch_n + 7) & ~7;
-        // work items of stage 2: (pixel, chunk of the batch).  One chunk keeps the reference's sequential per-pixel sum order and
-        // needs no partial buffers; small images are split so that every lane sees >= ~4 items (load balance at the tail).
-        int chunk = c->chunk_spp > 0 ? ((c->chunk_spp + 7) & ~7) : 0;
-        if (chunk <= 0) {
-            const u64 want = std::max<u64>(1, (4 * lanes) / n_pix);          // one chunk from ~530k pixels up (1280x720 and larger)
-            const int n_chunks = static_cast<int>(std::min<u64>(want, static_cast<u64>(p.hit_stride / 8)));
-            chunk = (((p.batch_n + n_chunks - 1) / n_chunks) + 7) & ~7;
+        // work items of stage 2: (pixel, chunk of the batch's samples), handed out chunk 0 first.  Chunk 0 adds to the pixel's running
+        // sum in place (the reference's sequential order); chunks 1.. produce partial sums that rt_combine_kernel adds in fixed order.
+        // The persistent kernel's tail is one item long, so: large images get one big chunk followed by a few 8-sample chunks (their
+        // items fill the machine while the big chunk's last items finish: tail 8 instead of batch_n samples, one partial buffer each);
+        // small images are split evenly so that every lane sees >= ~4 items.
+        int chunk0, chunk, n_chunks;
+        if (c->chunk_spp > 0) { chunk0 = chunk = (c->chunk_spp + 7) & ~7; n_chunks = (p.batch_n + chunk - 1) / chunk; }
+        else if (4 * lanes > n_pix) {
+            const u64 want = (4 * lanes) / n_pix;
+            const int nc = static_cast<int>(std::min<u64>(want, static_cast<u64>(p.hit_stride / 8)));
+            chunk0 = chunk = (((p.batch_n + nc - 1) / nc) + 7) & ~7; n_chunks = (p.batch_n + chunk - 1) / chunk;
+        } else {
+            // k tail chunks of 8 samples: their work (8 k frames over the whole image) must outlast the big chunk's last items
+            // (batch_n - 8 k samples of ONE pixel, ~80 us each at depth 50 on the default scene): with rho = item time per
+            // sample / image time per sample ~ 127000 / n_pix, k >= batch_n rho / (8 (1 + rho)).  From ~6 Mpixel up the tail is
+            // under 2 % of the launch and the batch stays one chunk.
+            const double rho = 127000.0 / static_cast<double>(n_pix);
+            int k = rho < 0.02 ? 0 : static_cast<int>(std::ceil(p.batch_n * rho / (8.0 * (1.0 + rho))));
+            k = std::min(std::min(k, 4), p.hit_stride / 8 - 1);
+            chunk = 8; chunk0 = p.hit_stride - 8 * k; n_chunks = 1 + k;
         }
-        p.chunk_spp = chunk; p.n_chunks = (p.batch_n + chunk - 1) / chunk;
+        p.chunk0_spp = chunk0; p.chunk_spp = chunk; p.n_chunks = n_chunks;
         p.partial = nullptr;
-        if (p.n_chunks > 1) { if (int r = ensure_partial(c, n_pix, p.n_chunks)) return r; p.partial = c->partial; }
+        if (n_chunks > 1) { if (int r = ensure_partial(c, n_pix, n_chunks - 1)) return r; p.partial = c->partial; }
         void* args[] = {&p};
         RT_CUDA(cudaLaunchKernel(k_first, dim3(grid), dim3(tpb), args, smem, c->stream));
         ++c->launches;
@@ -954,7 +967,7 @@ static int render_two_stage(rt_context* c, rt::RenderParams& p, int spp, int max
             RT_CUDA(cudaLaunchKernel(k_path, dim3(grid), dim3(tpb), args, smem, c->stream));
             ++c->launches;
             if (p.n_chunks > 1) {
-                rt::rt_combine_kernel<<<static_cast<unsigned>((n_pix + 255) / 256), 256, 0, c->stream>>>(p.hdr, p.partial, p.n_chunks, n_pix, p.overwrite);
+                rt::rt_combine_kernel<<<static_cast<unsigned>((n_pix + 255) / 256), 256, 0, c->stream>>>(p.hdr, p.partial, p.n_chunks - 1, n_pix, 0);
                 ++c->launches;
             }
         }

@@ -45,6 +45,8 @@ struct RenderParams {
     uint16_t* hits;              // [W*H][hit_stride]: slot + 1 of the sphere the primary ray of (pixel, batch sample) hits, 0 = sky
     int hit_stride;              // samples per row: batch_n rounded up to a multiple of 8 (rows are 16-byte aligned)
     int batch_s0, batch_n;
+    int chunk0_spp;              // stage 2: samples of chunk 0 of the batch (accumulated straight into hdr); chunks 1.. have chunk_spp samples
+                                 // each and go through partial[chunk - 1].  Both are multiples of 8 (record alignment)
     int overwrite;               // 1: this launch starts the running sum (no read of hdr): RT_FLAG_OVERWRITE, first batch of the call
 };
 
@@ -472,9 +474,10 @@ __global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : RT_MAX
                     if (item >= n_items) st = PS_DONE;
                     else if (item_to_pixel(p, item, chunk, px, py)) {
                         pix = py * p.W + px;
-                        s_cur = chunk * p.chunk_spp;                         // chunk_spp is a multiple of 8: records stay aligned
-                        s_end = min(p.batch_n, s_cur + p.chunk_spp);
-                        acc = (p.n_chunks == 1 && !p.overwrite) ? p.hdr[pix] : make_float4(0.f, 0.f, 0.f, 0.f);
+                        // chunk 0 continues the pixel's running sum in place; later chunks start partial sums (multiples of 8: records stay aligned)
+                        s_cur = chunk == 0 ? 0 : p.chunk0_spp + (chunk - 1) * p.chunk_spp;
+                        s_end = min(p.batch_n, s_cur + (chunk == 0 ? p.chunk0_spp : p.chunk_spp));
+                        acc = (chunk == 0 && !p.overwrite) ? p.hdr[pix] : make_float4(0.f, 0.f, 0.f, 0.f);
                         st = PS_SCAN;
                     }
                 }
@@ -482,8 +485,8 @@ __global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : RT_MAX
             if (st == PS_SCAN) {
                 for (;;) {
                     if (s_cur >= s_end) {
-                        if (p.n_chunks == 1) p.hdr[pix] = acc;
-                        else p.partial[static_cast<size_t>(chunk) * n_pix + pix] = acc;
+                        if (chunk == 0) p.hdr[pix] = acc;
+                        else p.partial[static_cast<size_t>(chunk - 1) * n_pix + pix] = acc;
                         st = PS_NEED_ITEM;
                         break;
                     }

@@ -523,31 +523,48 @@ def test_several_lights_match_oracle(gpu, orc, flags_name):
 # ---------------------------------------------------------------- converged images vs the committed reference-build goldens
 @pytest.mark.parametrize("key,name,depth", [("c2", "d488", 0), ("c3", "d488", 50), ("c5", "s4096", 50)])
 def test_converged_image_matches_reference_golden(gpu, key, name, depth):
-    """BASELINE.json: converged linear radiance at 4096 spp, per-pixel relRMSE < 1e-2 and image-mean relative error < 0.5 %.
-    The golden is the reference's OWN renderer (oracle/_ref: its common-lib sources, atomic Halton sampler, BVH) at 4096 spp and
-    1/8 scale (tests/golden/make_golden_converged.py); the bar is stated next to the Monte Carlo noise floor stored with it
-    (two oracle seeds at the same spp): where the floor itself exceeds 1e-2 the 1e-2 bar is not resolvable at this spp and the
-    test asserts 'within 1.5x the floor + 1e-2' instead of pretending."""
+    """BASELINE.json's statistical bar, asserted as stated: converged linear radiance, per-pixel relRMSE < 1e-2 and image-mean
+    relative error < 0.5 %.  The golden is the reference's OWN renderer (oracle/_ref: its common-lib sources, atomic Halton
+    sampler, BVH) at 65,536 spp and 1/8 scale (tests/golden/make_golden_converged.py); the GPU renders the same frames with its
+    counter RNG.  At this sample count the Monte Carlo noise left in either image (~0.003, stored with the golden as a
+    diagnostic) is far below the bar, so a systematic bias of a percent in the sampler substitution, pow_lobe or the pinned
+    sincos would fail here."""
     import os
     rt = gpu
     path = os.path.join(os.path.dirname(__file__), "golden", "golden_converged.npz")
     gold = np.load(path)
+    spp = int(gold["spp"])
+    assert spp >= 65536
     ref = gold[key + "_mean"].astype(np.float64) * 1024.0
-    floor = float(gold[key + "_floor"])
+    noise = float(gold[key + "_floor"])
     h, w = ref.shape[:2]
-    spp = 4096
     scene = rt.scenes.NAMED[name]()
     r = _renderer(rt, scene, rt.scenes.default_camera(aspect=w / h), w, h)
-    r.render(spp, depth, rt.RT_FLAG_ACCEL)          # same bits as brute force (test_accel_*), 6x faster on s4096
+    r.render(spp, depth, rt.RT_FLAG_ACCEL)          # same bits as brute force (test_accel_*), several times faster on s4096
     g = r.read_hdr_sum()
     assert np.all(g[..., 3] == spp)
     mean = g[..., :3].astype(np.float64) / spp * 2.0 ** 15
     got, merr = rel_rmse(mean, ref), mean_rel_err(mean, ref)
-    print(f"{key}: relRMSE gpu-vs-reference-golden {got:.4f} (noise floor {floor:.4f}); image-mean rel err {merr:.5f}")
+    print(f"{key}: relRMSE gpu-vs-reference-golden {got:.5f} at {spp} spp (noise left in the golden ~{noise:.5f}); image-mean rel err {merr:.6f}")
+    _record_rmse(key, {"rel_rmse": got, "mean_rel_err": merr, "golden_noise_estimate": noise, "spp": spp, "scale": f"{w}x{h}"})
+    assert noise < 4e-3                              # the bar is resolvable
     assert merr < 5e-3
-    assert got < 1.5 * floor + 1e-2
-    if floor < 2e-3:
-        assert got < 1e-2                            # resolvable: the BASELINE bar itself
+    assert got < 1e-2
+
+
+def _record_rmse(key, entry):
+    """pytest -q swallows the print: keep what the GPU scored in a file (gpurun_out/ travels back from the GPU box)."""
+    import json
+    import os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = os.path.join(root, "gpurun_out", "rmse_gpu_tests.json")
+    try:
+        os.makedirs(os.path.dirname(out), exist_ok=True)
+        data = json.load(open(out)) if os.path.exists(out) else {}
+        data[key] = entry
+        json.dump(data, open(out, "w"), indent=1)
+    except OSError:
+        pass
 
 
 # ---------------------------------------------------------------- round 2: schedule, overwrite, asynchrony, metal alpha
@@ -615,7 +632,7 @@ def test_render_call_is_asynchronous(gpu, scene_factory):
     rt = gpu
     scene, _ = scene_factory("d488")
     r = _renderer(rt, scene, rt.scenes.default_camera(aspect=16 / 9), 1280, 720)
-    r.render(8, 50); r.synchronize()                       # warm-up: allocations, module load
+    r.render(128, 50); r.synchronize(); r.clear()          # warm-up: module load, first-hit record / table allocations (grow-only)
     t0 = time.perf_counter()
     r.render(128, 50)
     t_call = time.perf_counter() - t0
@@ -623,7 +640,7 @@ def test_render_call_is_asynchronous(gpu, scene_factory):
     t_total = time.perf_counter() - t0
     assert t_total > 0.03, t_total                         # ~70 ms of device work
     assert t_call < 0.25 * t_total, (t_call, t_total)
-    assert np.all(r.read_hdr_sum()[..., 3] == 136)
+    assert np.all(r.read_hdr_sum()[..., 3] == 128)
 
 
 def test_metal_alpha_lane_matches_oracle(gpu, orc):
