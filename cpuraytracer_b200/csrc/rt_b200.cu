@@ -255,6 +255,7 @@ struct rt_context {
     float4* partial = nullptr; size_t partial_bytes = 0;
     uint16_t* hits = nullptr; size_t hits_bytes = 0;   // first-hit records of one batch (two-stage schedule)
     int path_tpb = 0, path_bps = 0;                    // CTA size / resident CTAs per SM of the stage-2 kernel
+    bool global_scene = false;                         // the sphere list does not fit one CTA's shared memory: kernels read it from global memory
     int accel_gshift_min = 3;                          // finest group size rt_set_scene tries (rt_set_accel_group_slots)
     float2 *jitter = nullptr, *lens = nullptr; size_t jitter_cap = 0, lens_cap = 0;
     u64* counters = nullptr;   // [0] work counter, [1..4] stats
@@ -311,8 +312,8 @@ template <class T> static int dev_realloc(T*& p, size_t n) {
 }
 static size_t scene_smem_bytes(int n_pad) { return static_cast<size_t>(n_pad / 2) * 40u + static_cast<size_t>(n_pad) * 4u; }
 // scene arrays + the per-thread candidate lists (2 lists x RT_LIST_CAP words), see stage_scene()
-static size_t cta_smem_bytes(int n_pad, int tpb) {
-    size_t b = scene_smem_bytes(n_pad) + static_cast<size_t>(tpb) * 2u * RT_LIST_CAP * 4u;
+static size_t cta_smem_bytes(int n_pad, int tpb, bool global_scene = false) {
+    size_t b = (global_scene ? 0u : scene_smem_bytes(n_pad)) + static_cast<size_t>(tpb) * 2u * RT_LIST_CAP * 4u;
 #if RT_FLAT_EXACT
     b += static_cast<size_t>((tpb + 31) / 32) * RT_WQ_BYTES_PER_WARP;       // per-warp candidate queue of the exact-test phase
 #endif
@@ -350,11 +351,13 @@ template <int G> static const void* accel_path_fn(bool halton, bool direct) {
 static const void* path_kernel(int mode, bool halton, int gshift, bool direct) {
     if (mode == rt::MODE_ACCEL) return gshift == 3 ? accel_path_fn<3>(halton, direct) : gshift == 4 ? accel_path_fn<4>(halton, direct) : accel_path_fn<5>(halton, direct);
     if (mode == rt::MODE_NO_CULL) return RT_FN(rt::rt_path_kernel<rt::MODE_NO_CULL, false, 5, false>);
+    if (mode == rt::MODE_CULL_GLOBAL) return direct ? RT_FN(rt::rt_path_kernel<rt::MODE_CULL_GLOBAL, false, 5, true>) : RT_FN(rt::rt_path_kernel<rt::MODE_CULL_GLOBAL, false, 5, false>);
     if (halton) return RT_FN(rt::rt_path_kernel<rt::MODE_CULL, true, 5, false>);
     return direct ? RT_FN(rt::rt_path_kernel<rt::MODE_CULL, false, 5, true>) : RT_FN(rt::rt_path_kernel<rt::MODE_CULL, false, 5, false>);
 }
 static const void* first_hit_kernel(int mode, int gshift) {
     if (mode == rt::MODE_ACCEL) return gshift == 3 ? RT_FN(rt::rt_first_hit_kernel<rt::MODE_ACCEL, 3>) : gshift == 4 ? RT_FN(rt::rt_first_hit_kernel<rt::MODE_ACCEL, 4>) : RT_FN(rt::rt_first_hit_kernel<rt::MODE_ACCEL, 5>);
+    if (mode == rt::MODE_CULL_GLOBAL) return RT_FN(rt::rt_first_hit_kernel<rt::MODE_CULL_GLOBAL, 5>);
     return mode == rt::MODE_NO_CULL ? RT_FN(rt::rt_first_hit_kernel<rt::MODE_NO_CULL, 5>) : RT_FN(rt::rt_first_hit_kernel<rt::MODE_CULL, 5>);
 }
 // Opt every kernel of a mode in to the large dynamic shared memory carve-out.
@@ -608,8 +611,9 @@ int rt_set_scene(rt_context* c, const rt_scene* s) {
     const int n = static_cast<int>(s->spheres.size());
     const int n_pad = std::max(32, (n + 31) / 32 * 32);
     const int np = n_pad / 2;
-    if (cta_smem_bytes(n_pad, 256) > static_cast<size_t>(c->prop.sharedMemPerBlockOptin))
-        return fail(RT_ERR_UNSUPPORTED, "rt_set_scene: %d spheres need %zu B of shared memory per CTA, device limit is %zu", n, cta_smem_bytes(n_pad, 256), static_cast<size_t>(c->prop.sharedMemPerBlockOptin));
+    if (n > 65534) return fail(RT_ERR_UNSUPPORTED, "rt_set_scene: %d spheres; the first-hit records index spheres with 16 bits (at most 65534)", n);
+    // a list that does not fit next to the candidate lists of a 256-thread CTA stays in global memory (slower, any size)
+    c->global_scene = cta_smem_bytes(n_pad, 256) > static_cast<size_t>(c->prop.sharedMemPerBlockOptin);
     const bool has_light = !s->lights.empty();
     host::V3 Ln{0.f, 0.f, 0.f};
     if (has_light) Ln = host::normalize3({s->lights[0].dir[0], s->lights[0].dir[1], s->lights[0].dir[2]});   // light.cpp:7
@@ -715,22 +719,29 @@ int rt_set_scene(rt_context* c, const rt_scene* s) {
     RT_CUDA(cudaFuncSetAttribute(rt::wf_intersect_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
     if (int r = optin_smem(rt::MODE_CULL, 5, optin)) return r;
     if (int r = optin_smem(rt::MODE_NO_CULL, 5, optin)) return r;
+    if (int r = optin_smem(rt::MODE_CULL_GLOBAL, 5, optin)) return r;
+    RT_CUDA(cudaFuncSetAttribute(rt::rt_primary_kernel<rt::MODE_CULL_GLOBAL>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
     int best_tpb = 0, best_bps = 0;
     c->path_tpb = 0; c->path_bps = 0;
+    const int scene_mode = c->global_scene ? rt::MODE_CULL_GLOBAL : rt::MODE_CULL;
     for (int tpb = 128; tpb <= RT_MAX_TPB; tpb += 128) {
-        const size_t smem = cta_smem_bytes(n_pad, tpb);
+        const size_t smem = cta_smem_bytes(n_pad, tpb, c->global_scene);
         if (smem > static_cast<size_t>(optin)) break;
         int bps = 0;
-        RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, rt::rt_render_kernel<rt::MODE_CULL>, tpb, smem));
-        if (bps * tpb > best_bps * best_tpb) { best_tpb = tpb; best_bps = bps; }
-        RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, path_kernel(rt::MODE_CULL, false, 5, false), tpb, smem));
+        if (!c->global_scene) {                              // the one-kernel schedule and the wavefront layout stage the list: small scenes only
+            RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, rt::rt_render_kernel<rt::MODE_CULL>, tpb, smem));
+            if (bps * tpb > best_bps * best_tpb) { best_tpb = tpb; best_bps = bps; }
+        }
+        RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, path_kernel(scene_mode, false, 5, false), tpb, smem));
         if (bps * tpb > c->path_bps * c->path_tpb) { c->path_tpb = tpb; c->path_bps = bps; }
     }
+    if (c->global_scene) { best_tpb = c->path_tpb; best_bps = c->path_bps; }
     if (c->path_bps < 1) return fail(RT_ERR_UNSUPPORTED, "rt_set_scene: path kernel does not fit on an SM with %zu B shared memory", cta_smem_bytes(n_pad, 256));
     if (best_bps < 1) return fail(RT_ERR_UNSUPPORTED, "rt_set_scene: render kernel does not fit on an SM with %zu B shared memory", cta_smem_bytes(n_pad, 256));
     c->tpb = best_tpb;
     c->render_blocks_per_sm = best_bps;
-    RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&c->wf_bps, rt::wf_intersect_kernel<false>, best_tpb, cta_smem_bytes(n_pad, best_tpb)));
+    c->wf_bps = 1;
+    if (!c->global_scene) RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&c->wf_bps, rt::wf_intersect_kernel<false>, best_tpb, cta_smem_bytes(n_pad, best_tpb)));
     if (c->wf_bps < 1) c->wf_bps = 1;
     auto safe_inv = [](float d) { const float dd = std::fabs(d) < 1e-18f ? std::copysign(1e-18f, d) : d; return 1.0f / dd; };   // rt_bvh.cuh safe_inv
     b.iLx = safe_inv(b.Lx); b.iLy = safe_inv(b.Ly); b.iLz = safe_inv(b.Lz);
@@ -902,11 +913,11 @@ static int render_one_kernel(rt_context* c, rt::RenderParams& p, int spp, uint32
 static int render_two_stage(rt_context* c, rt::RenderParams& p, int spp, int max_depth, uint32_t flags) {
     const size_t n_pix = static_cast<size_t>(c->W) * c->H;
     const bool accel = (flags & RT_FLAG_ACCEL) != 0, halton = (flags & RT_FLAG_HALTON) != 0;
-    const int mode = accel ? rt::MODE_ACCEL : (flags & RT_FLAG_DEBUG_NO_CULL_) ? rt::MODE_NO_CULL : rt::MODE_CULL;
+    const int mode = accel ? rt::MODE_ACCEL : (flags & RT_FLAG_DEBUG_NO_CULL_) ? rt::MODE_NO_CULL : c->global_scene ? rt::MODE_CULL_GLOBAL : rt::MODE_CULL;
     const int gshift = accel ? p.accel.gshift : 5;
     const bool direct = max_depth == 0 && !halton && mode != rt::MODE_NO_CULL;
     const int tpb = accel ? c->accel_tpb : c->path_tpb, bps = accel ? c->accel_bps : c->path_bps;
-    const size_t smem = accel ? accel_cta_smem_bytes(p.accel, tpb) : cta_smem_bytes(c->n_pad, tpb);
+    const size_t smem = accel ? accel_cta_smem_bytes(p.accel, tpb) : cta_smem_bytes(c->n_pad, tpb, c->global_scene);
     const int grid = c->prop.multiProcessorCount * bps;
     const void* k_first = first_hit_kernel(mode, gshift);
     const void* k_path = path_kernel(mode, halton, gshift, direct);
@@ -990,6 +1001,8 @@ int rt_render(rt_context* c, uint64_t first_sample, int spp, int max_depth, uint
     if ((flags & RT_FLAG_WAVEFRONT) && max_depth >= (1 << 22)) return fail(RT_ERR_INVALID_ARGUMENT, "rt_render: the wavefront layout packs the depth into 23 bits");
     if (!c->extra_lights.empty() && (flags & RT_FLAG_WAVEFRONT))
         return fail(RT_ERR_UNSUPPORTED, "rt_render: scenes with more than one light do not run on the wavefront layout");
+    if (c->global_scene && !(flags & RT_FLAG_ACCEL) && (one_kernel || (flags & (RT_FLAG_HALTON | RT_FLAG_DEBUG_NO_CULL_))))
+        return fail(RT_ERR_UNSUPPORTED, "rt_render: %d spheres do not fit in shared memory; such scenes run on the default two-stage schedule with the counter RNG only", c->n_spheres);
     if (spp == 0) return RT_OK;
     if (int r = ctx_use(c)) return r;
     rt::RenderParams p;
@@ -1048,8 +1061,9 @@ int rt_primary_hits(rt_context* c, uint64_t sample, uint32_t flags, int32_t* sph
     rt::RenderParams p;
     if (int r = prepare_frames(c, sample, 1, 0, flags, p)) return r;
     p.chunk_spp = 1; p.n_chunks = 1;
-    const size_t smem = cta_smem_bytes(c->n_pad, c->tpb);
+    const size_t smem = cta_smem_bytes(c->n_pad, c->tpb, c->global_scene);
     const int grid = c->prop.multiProcessorCount * std::max(1, c->render_blocks_per_sm);
+    if (c->global_scene && (flags & RT_FLAG_DEBUG_NO_CULL_)) return fail(RT_ERR_UNSUPPORTED, "rt_primary_hits: the no-cull debug mode stages the sphere list in shared memory (small scenes only)");
     if ((flags & RT_FLAG_ACCEL) && !c->accel_ok) return fail(RT_ERR_UNSUPPORTED, "rt_primary_hits: RT_FLAG_ACCEL unavailable for this scene: %s", c->accel_why.c_str());
     if (flags & RT_FLAG_ACCEL) {
         int32_t* a_ids = c->ids; int32_t* a_mids = c->mids;
@@ -1058,6 +1072,7 @@ int rt_primary_hits(rt_context* c, uint64_t sample, uint32_t flags, int32_t* sph
                                  accel_cta_smem_bytes(p.accel, c->accel_tpb), c->stream));
     }
     else if (flags & RT_FLAG_DEBUG_NO_CULL_) rt::rt_primary_kernel<rt::MODE_NO_CULL><<<grid, c->tpb, smem, c->stream>>>(p, c->ids, c->mids);
+    else if (c->global_scene) rt::rt_primary_kernel<rt::MODE_CULL_GLOBAL><<<grid, c->tpb, smem, c->stream>>>(p, c->ids, c->mids);
     else rt::rt_primary_kernel<rt::MODE_CULL><<<grid, c->tpb, smem, c->stream>>>(p, c->ids, c->mids);
     ++c->launches;
     RT_CUDA(cudaGetLastError());

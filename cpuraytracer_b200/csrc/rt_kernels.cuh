@@ -71,8 +71,16 @@ enum LaneState { ST_NEED_ITEM = 0, ST_NEW_PATH = 1, ST_IN_PATH = 2, ST_DONE = 3 
 #else
 #define RT_RENDER_BOUNDS __launch_bounds__(RT_MAX_TPB)
 #endif
+// GLOBAL_SCENE (MODE_CULL_GLOBAL): a sphere list too large for one CTA's shared memory is read in place from global memory
+// (broadcast loads through L1 / L2; every lane of a warp reads the same address) and shared memory holds the candidate lists only.
+template <bool GLOBAL_SCENE = false>
 __device__ __forceinline__ void stage_scene(const RenderParams& p, float4*& sA, float4*& sB, float2*& sC, float*& sR, uint32_t*& lists, unsigned char* smem) {
     const int np = p.n_pairs_pad;
+    if constexpr (GLOBAL_SCENE) {
+        sA = const_cast<float4*>(p.cullA); sB = const_cast<float4*>(p.cullB); sC = const_cast<float2*>(p.cullC); sR = const_cast<float*>(p.radius);
+        lists = reinterpret_cast<uint32_t*>(smem) + threadIdx.x;
+        return;
+    }
     sA = reinterpret_cast<float4*>(smem);
     sB = sA + np;
     sC = reinterpret_cast<float2*>(sB + np);
@@ -203,7 +211,7 @@ __device__ __forceinline__ bool item_to_pixel(const RenderParams& p, u64 item, i
 
 // MODE: 0 = brute force with the conservative cull (default), 1 = brute force, every sphere through the exact test
 // (debug: proves the cull is result-neutral), 2 = RT_FLAG_ACCEL box hierarchy in front of the same cull (rt_bvh.cuh).
-enum { MODE_CULL = 0, MODE_NO_CULL = 1, MODE_ACCEL = 2 };
+enum { MODE_CULL = 0, MODE_NO_CULL = 1, MODE_ACCEL = 2, MODE_CULL_GLOBAL = 3 };   // 3 = MODE_CULL with the sphere list left in global memory (stage_scene)
 #ifndef RT_ACCEL_MAX_TPB
 #define RT_ACCEL_MAX_TPB 640
 #endif
@@ -370,7 +378,7 @@ __global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : RT_MAX
     float4 *sA = nullptr, *sB = nullptr; float2* sC = nullptr; float* sR = nullptr; uint32_t* lists = nullptr;
     AccelSmem av{};
     if constexpr (MODE == MODE_ACCEL) av = stage_accel(p.accel, smem);
-    else stage_scene(p, sA, sB, sC, sR, lists, smem);
+    else stage_scene<MODE == MODE_CULL_GLOBAL>(p, sA, sB, sC, sR, lists, smem);
     AccelCounters acnt; acnt.group_visits = 0u;
     const unsigned FULL = 0xffffffffu;
     const unsigned lane = threadIdx.x & 31u;
@@ -436,7 +444,7 @@ __global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : RT_MAX
     if constexpr (MODE == MODE_ACCEL) {
         av = stage_accel(p.accel, smem);
         sA = const_cast<float4*>(av.sA); sB = const_cast<float4*>(av.sB); sR = const_cast<float*>(av.sR);
-    } else stage_scene(p, sA, sB, sC, sR, lists, smem);
+    } else stage_scene<MODE == MODE_CULL_GLOBAL>(p, sA, sB, sC, sR, lists, smem);
     const int lstride = static_cast<int>(blockDim.x);
     const V3 invL = mk3(p.iLx, p.iLy, p.iLz);
     AccelCounters acnt; acnt.group_visits = 0u;
@@ -677,7 +685,7 @@ __global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : RT_MAX
     float4 *sA = nullptr, *sB = nullptr; float2* sC = nullptr; float* sR = nullptr; uint32_t* lists = nullptr;
     AccelSmem av{};
     if constexpr (MODE == MODE_ACCEL) av = stage_accel(p.accel, smem);
-    else stage_scene(p, sA, sB, sC, sR, lists, smem);
+    else stage_scene<MODE == MODE_CULL_GLOBAL>(p, sA, sB, sC, sR, lists, smem);
     AccelCounters acnt; acnt.group_visits = 0u;
     const u64 n_items = static_cast<u64>(p.tiles_x) * p.tiles_y * 32ull;
     for (u64 item = blockIdx.x * static_cast<u64>(blockDim.x) + threadIdx.x; item < ((n_items + 31ull) & ~31ull); item += static_cast<u64>(gridDim.x) * blockDim.x) {

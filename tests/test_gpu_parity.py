@@ -674,3 +674,33 @@ def test_metal_alpha_lane_matches_oracle(gpu, orc):
     flat.textures["c0"][:, 3] = 1.0; flat.textures["c1"][:, 3] = 1.0
     _, ost1 = orc.render(orc.Scene.from_flat(flat), orc_camera(orc, cam), orc.config(w, h, spp=spp))
     assert ost1.closest_rays > ost.closest_rays
+
+
+def test_scene_larger_than_shared_memory_renders_from_global_memory(gpu, orc):
+    """The reference accepts any sphere count.  A list that does not fit one CTA's shared memory (~9k spheres) is read in place
+    from global memory by the same kernels (MODE_CULL_GLOBAL): primary hits bit-exact and paths identical to the oracle; the
+    box hierarchy (8192 small spheres at most) and the debug schedules say so loudly instead of rendering something else."""
+    rt = gpu
+    rng = np.random.default_rng(23)
+    scene = _random_scene(rt, rng, 12000, 4.0, 40.0, True)
+    osc = orc.Scene.from_flat(scene.export())
+    w, h, spp = 96, 54, 2
+    cam = rt.Camera((30.0, 6.0, -14.0), (0.0, 1.0, 0.0), 40.0, w / h, 30.0, 0.3)
+    r = _renderer(rt, scene, cam, w, h)
+    flags = rt.RT_FLAG_JITTER_OFF | rt.RT_FLAG_LENS_OFF
+    ids, mids = r.primary_hits(1, flags)
+    oids, omids = orc.primary_hits(osc, orc_camera(orc, cam), orc.config(w, h, flags=flags))
+    assert np.array_equal(ids, oids) and np.array_equal(mids, omids) and (ids >= 0).mean() > 0.5
+    r.reset_stats(); r.render(spp, 6)
+    g, st = r.read_hdr_sum(), r.stats()
+    o, ost = orc.render(osc, orc_camera(orc, cam), orc.config(w, h, spp=spp, max_depth=6))
+    assert (st.paths, st.closest_rays, st.shadow_rays) == (ost.paths, ost.closest_rays, ost.shadow_rays)
+    assert st.sphere_tests == 12001 * (st.closest_rays + st.shadow_rays - 0) or st.sphere_tests <= 12001 * (st.closest_rays + st.shadow_rays)
+    assert _close(g, o) < RTOL
+    r.clear(); r.render(spp, 0)                                   # the shadow-only path kernel on a global list
+    o0, _ = orc.render(osc, orc_camera(orc, cam), orc.config(w, h, spp=spp, max_depth=0))
+    assert _close(r.read_hdr_sum(), o0) < RTOL
+    for bad in (rt.RT_FLAG_ACCEL, rt.RT_FLAG_DEBUG_ONE_KERNEL, rt.RT_FLAG_WAVEFRONT, rt.RT_FLAG_HALTON, rt.RT_FLAG_DEBUG_NO_CULL):
+        with pytest.raises(rt.RtError) as e:
+            r.render(1, 2, bad)
+        assert e.value.code == 5, bad                             # RT_ERR_UNSUPPORTED
