@@ -922,10 +922,10 @@ static int render_two_stage(rt_context* c, rt::RenderParams& p, int spp, int max
     const void* k_first = first_hit_kernel(mode, gshift);
     const void* k_path = path_kernel(mode, halton, gshift, direct);
     // batch: as many frames as fit first-hit records of max(256 MiB, two running-sum buffers) (2 B per pixel and frame), a
-    // multiple of 8, at most 4096: 64 frames at 1920x1080, 16 at 3840x2160 -- the records are the only per-batch allocation
+    // multiple of 16, at most 4096: 64 frames at 1920x1080, 16 at 3840x2160 -- the records are the only per-batch allocation
     const size_t cap_bytes = std::max<size_t>(256ull << 20, n_pix * 32);
-    int batch = static_cast<int>(std::min<size_t>(4096, std::max<size_t>(8, (cap_bytes / (n_pix * 2)) & ~static_cast<size_t>(7))));
-    batch = std::min(batch, (spp + 7) & ~7);
+    int batch = static_cast<int>(std::min<size_t>(4096, std::max<size_t>(16, (cap_bytes / (n_pix * 2)) & ~static_cast<size_t>(15))));
+    batch = std::min(batch, (spp + 15) & ~15);
     const size_t hits_need = n_pix * static_cast<size_t>(batch) * sizeof(uint16_t);
     if (c->hits_bytes < hits_need) {
         if (c->hits) { RT_CUDA(cudaStreamSynchronize(c->stream)); cudaFree(c->hits); c->hits = nullptr; c->hits_bytes = 0; }
@@ -937,7 +937,7 @@ static int render_two_stage(rt_context* c, rt::RenderParams& p, int spp, int max
     const u64 lanes = static_cast<u64>(grid) * tpb;
     for (int s0 = 0; s0 < spp; s0 += batch) {
         p = base;
-        p.batch_s0 = s0; p.batch_n = std::min(batch, spp - s0); p.hit_stride = (p.batch_n + 7) & ~7;
+        p.batch_s0 = s0; p.batch_n = std::min(batch, spp - s0); p.hit_stride = (p.batch_n + 15) & ~15;
         // work items of stage 2: (pixel, chunk of the batch's samples), handed out chunk 0 first.  Chunk 0 adds to the pixel's running
         // sum in place (the reference's sequential order); chunks 1.. produce partial sums that rt_combine_kernel adds in fixed order.
         // The persistent kernel's tail is one item long, so: large images get one big chunk followed by a few 8-sample chunks (their
@@ -947,7 +947,7 @@ static int render_two_stage(rt_context* c, rt::RenderParams& p, int spp, int max
         if (c->chunk_spp > 0) { chunk0 = chunk = (c->chunk_spp + 7) & ~7; n_chunks = (p.batch_n + chunk - 1) / chunk; }
         else if (4 * lanes > n_pix) {
             const u64 want = (4 * lanes) / n_pix;
-            const int nc = static_cast<int>(std::min<u64>(want, static_cast<u64>(p.hit_stride / 8)));
+            const int nc = static_cast<int>(std::min<u64>(want, static_cast<u64>((p.batch_n + 7) / 8)));
             chunk0 = chunk = (((p.batch_n + nc - 1) / nc) + 7) & ~7; n_chunks = (p.batch_n + chunk - 1) / chunk;
         } else {
             // k tail chunks of 8 samples: their work (8 k frames over the whole image) must outlast the big chunk's last items
@@ -956,8 +956,9 @@ static int render_two_stage(rt_context* c, rt::RenderParams& p, int spp, int max
             // under 2 % of the launch and the batch stays one chunk.
             const double rho = 127000.0 / static_cast<double>(n_pix);
             int k = rho < 0.02 ? 0 : static_cast<int>(std::ceil(p.batch_n * rho / (8.0 * (1.0 + rho))));
-            k = std::min(std::min(k, 4), p.hit_stride / 8 - 1);
-            chunk = 8; chunk0 = p.hit_stride - 8 * k; n_chunks = 1 + k;
+            const int n8 = (p.batch_n + 7) / 8;                 // 8-sample groups that hold samples
+            k = std::min(std::min(k, 4), n8 - 1);
+            chunk = 8; chunk0 = 8 * (n8 - k); n_chunks = 1 + k;
         }
         p.chunk0_spp = chunk0; p.chunk_spp = chunk; p.n_chunks = n_chunks;
         p.partial = nullptr;

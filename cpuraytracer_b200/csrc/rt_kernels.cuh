@@ -43,7 +43,7 @@ struct RenderParams {
     // two-stage schedule (rt_first_hit_kernel + rt_path_kernel): one launch pair renders the batch of frames
     // [first_sample + batch_s0, first_sample + batch_s0 + batch_n); chunk_spp / n_chunks then split the BATCH into work items
     uint16_t* hits;              // [W*H][hit_stride]: slot + 1 of the sphere the primary ray of (pixel, batch sample) hits, 0 = sky
-    int hit_stride;              // samples per row: batch_n rounded up to a multiple of 8 (rows are 16-byte aligned)
+    int hit_stride;              // samples per row: batch_n rounded up to a multiple of 16 (rows are whole 32-byte sectors)
     int batch_s0, batch_n;
     int chunk0_spp;              // stage 2: samples of chunk 0 of the batch (accumulated straight into hdr); chunks 1.. have chunk_spp samples
                                  // each and go through partial[chunk - 1].  Both are multiples of 8 (record alignment)
@@ -371,7 +371,7 @@ __global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : RT_MAX
 // Arithmetic per path is unchanged (same device functions, same order), so the bits are those of the one-kernel schedule.
 // ------------------------------------------------------------------------------------------------------------------
 
-// Stage 1.  Work item of a WARP = (8x4 pixel tile, group of 8 consecutive batch samples); static round-robin over the grid.
+// Stage 1.  Work item of a WARP = (8x4 pixel tile, group of 16 consecutive batch samples); static round-robin over the grid.
 template <int MODE, int GSHIFT = 5>
 __global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : RT_MAX_TPB) rt_first_hit_kernel(const RenderParams p) {
     extern __shared__ __align__(256) unsigned char smem[];
@@ -384,7 +384,7 @@ __global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : RT_MAX
     const unsigned lane = threadIdx.x & 31u;
     const V3 Ldir = mk3(p.Lx, p.Ly, p.Lz);
     const u64 n_tiles = static_cast<u64>(p.tiles_x) * p.tiles_y;
-    const u64 n_items = n_tiles * static_cast<u64>(p.hit_stride >> 3);
+    const u64 n_items = n_tiles * static_cast<u64>(p.hit_stride >> 4);
     const u64 n_warps = (static_cast<u64>(gridDim.x) * blockDim.x) >> 5;
     uint32_t n_closest = 0, n_pass = 0;
     for (u64 item = (static_cast<u64>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5; item < n_items; item += n_warps) {
@@ -393,10 +393,10 @@ __global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : RT_MAX
         const int px = static_cast<int>((tile % p.tiles_x) * 8u + (lane & 7u));
         const int py = static_cast<int>((tile / p.tiles_x) * 4u + (lane >> 3));
         const bool valid = px < p.W && py < p.H;
-        u64 rec_lo = 0ull, rec_hi = 0ull;
+        u64 rec0 = 0ull, rec1 = 0ull, rec2 = 0ull, rec3 = 0ull;      // 16 records of this lane's pixel = one 32-byte sector
 #pragma unroll 1
-        for (int k = 0; k < 8; ++k) {
-            const int sb = g * 8 + k;                        // sample index inside the batch
+        for (int k = 0; k < 16; ++k) {
+            const int sb = g * 16 + k;                       // sample index inside the batch
             if (sb >= p.batch_n) break;                      // warp-uniform
             const int s = p.batch_s0 + sb;                   // index into the per-call Halton tables
             V3 o = mk3(0.f, 0.f, 0.f), d = mk3(0.f, 0.f, 1.f);
@@ -413,13 +413,14 @@ __global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : RT_MAX
             if constexpr (MODE == MODE_ACCEL) q = fused_query_accel<GSHIFT, RAYS_CLOSEST>(av, p.accel, static_cast<int>(blockDim.x), o, d, Ldir, mk3(p.iLx, p.iLy, p.iLz), valid, false, acnt);
             else q = fused_query<MODE == MODE_NO_CULL, RAYS_CLOSEST>(sA, sB, sC, sR, lists, static_cast<int>(blockDim.x), p.n_groups, p.n_spheres, o, d, Ldir, valid, false);
             ++n_pass;
-            const u64 v16 = (valid && q.idx >= 0) ? static_cast<u64>(((MODE == MODE_ACCEL) ? q.slot : q.idx) + 1) : 0ull;
-            if (k < 4) rec_lo |= v16 << (16 * k); else rec_hi |= v16 << (16 * (k - 4));
+            const u64 v16 = ((valid && q.idx >= 0) ? static_cast<u64>(((MODE == MODE_ACCEL) ? q.slot : q.idx) + 1) : 0ull) << (16 * (k & 3));
+            if (k < 4) rec0 |= v16; else if (k < 8) rec1 |= v16; else if (k < 12) rec2 |= v16; else rec3 |= v16;
         }
-        if (valid) {
+        if (valid) {                                         // two 16-byte stores into one aligned 32-byte sector: no partial-sector write reaches HBM
             const size_t pix = static_cast<size_t>(py) * p.W + px;
-            uint4 r; r.x = static_cast<uint32_t>(rec_lo); r.y = static_cast<uint32_t>(rec_lo >> 32); r.z = static_cast<uint32_t>(rec_hi); r.w = static_cast<uint32_t>(rec_hi >> 32);
-            *reinterpret_cast<uint4*>(p.hits + pix * p.hit_stride + static_cast<size_t>(g) * 8) = r;
+            uint4* dst = reinterpret_cast<uint4*>(p.hits + pix * p.hit_stride + static_cast<size_t>(g) * 16);
+            dst[0] = make_uint4(static_cast<uint32_t>(rec0), static_cast<uint32_t>(rec0 >> 32), static_cast<uint32_t>(rec1), static_cast<uint32_t>(rec1 >> 32));
+            dst[1] = make_uint4(static_cast<uint32_t>(rec2), static_cast<uint32_t>(rec2 >> 32), static_cast<uint32_t>(rec3), static_cast<uint32_t>(rec3 >> 32));
         }
     }
     u64 c0 = n_closest;

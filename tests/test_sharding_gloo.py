@@ -64,7 +64,7 @@ def _worker(rank, world, port, w, h, first, spp, out_path):
     dist.destroy_process_group()
 
 
-def _worker_multicall(rank, world, port, w, h, calls, out_path):
+def _worker_multicall(rank, world, port, w, h, calls, out_path, overwrite_capable=False):
     sys.path.insert(0, ROOT)
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     import torch
@@ -80,10 +80,16 @@ def _worker_multicall(rank, world, port, w, h, calls, out_path):
     hdr_np = np.zeros((h, w, 4), np.float32)
     hdr = torch.from_numpy(hdr_np)                       # shares memory: the oracle adds into the tensor gloo reduces
 
-    def render_into(my_first, my_spp):
+    def render_into(my_first, my_spp, overwrite=False):
+        if overwrite:                                    # what RT_FLAG_OVERWRITE does on the device: the call starts the sum
+            hdr_np[...] = 0.0
+        elif overwrite_capable and rank != 0:
+            raise AssertionError("ranks >= 1 must be asked to overwrite")
         orc.render(osc, cp, orc.config(w, h, spp=my_spp, first_sample=my_first, threads=1), hdr_np)
 
-    acc = ShardedAccumulator(hdr, render_into)
+    if overwrite_capable and rank != 0:
+        hdr_np[...] = 123.0                              # stale content the protocol must never add to rank 0
+    acc = ShardedAccumulator(hdr, render_into, overwrite_capable=overwrite_capable)
     for spp in calls:
         acc.render(spp)
     if rank == 0:
@@ -92,12 +98,15 @@ def _worker_multicall(rank, world, port, w, h, calls, out_path):
     dist.destroy_process_group()
 
 
-def test_consecutive_sharded_calls_accumulate_once(orc, rt, tmp_path):
-    """bench.py's loop: several render+reduce calls in a row.  Rank 0 must end with every frame exactly once."""
+@pytest.mark.parametrize("overwrite_capable,calls", [(False, (3, 2, 4)), (True, (3, 2, 4)), (True, (1, 1, 3))])
+def test_consecutive_sharded_calls_accumulate_once(orc, rt, tmp_path, overwrite_capable, calls):
+    """bench.py's loop: several render+reduce calls in a row.  Rank 0 must end with every frame exactly once -- with a renderer
+    that is cleared before each call on ranks >= 1, and with one that overwrites (RT_FLAG_OVERWRITE; a rank whose share of a
+    call is empty -- 1 frame over 2 ranks -- must still contribute zeros, not its stale buffer)."""
     import torch.multiprocessing as mp
-    w, h, calls = 40, 24, (3, 2, 4)
+    w, h = 40, 24
     out = str(tmp_path / "sum.npy")
-    mp.spawn(_worker_multicall, args=(2, _free_port(), w, h, calls, out), nprocs=2, join=True)
+    mp.spawn(_worker_multicall, args=(2, _free_port(), w, h, calls, out, overwrite_capable), nprocs=2, join=True)
     got = np.load(out)
     scene = rt.scenes.scene_small()
     osc = orc.Scene.from_flat(scene.export())
