@@ -940,27 +940,28 @@ static int render_two_stage(rt_context* c, rt::RenderParams& p, int spp, int max
         p.batch_s0 = s0; p.batch_n = std::min(batch, spp - s0); p.hit_stride = (p.batch_n + 15) & ~15;
         // work items of stage 2: (pixel, chunk of the batch's samples), handed out chunk 0 first.  Chunk 0 adds to the pixel's running
         // sum in place (the reference's sequential order); chunks 1.. produce partial sums that rt_combine_kernel adds in fixed order.
-        // The persistent kernel's tail is one item long, so: large images get one big chunk followed by a few 8-sample chunks (their
-        // items fill the machine while the big chunk's last items finish: tail 8 instead of batch_n samples, one partial buffer each);
-        // small images are split evenly so that every lane sees >= ~4 items.
-        int chunk0, chunk, n_chunks;
-        if (c->chunk_spp > 0) { chunk0 = chunk = (c->chunk_spp + 7) & ~7; n_chunks = (p.batch_n + chunk - 1) / chunk; }
+        // The persistent kernel's tail is one item long, so large images get chunks of halving size (one partial buffer per chunk after
+        // the first); small images are split evenly so that every lane sees >= ~4 items.
+        int chunk = 8, n_chunks = 1;
+        p.n_ladder = 0;
+        const int n8 = (p.batch_n + 7) / 8;                     // 8-sample groups that hold samples
+        if (c->chunk_spp > 0) { chunk = (c->chunk_spp + 7) & ~7; n_chunks = (p.batch_n + chunk - 1) / chunk; }
         else if (4 * lanes > n_pix) {
             const u64 want = (4 * lanes) / n_pix;
-            const int nc = static_cast<int>(std::min<u64>(want, static_cast<u64>((p.batch_n + 7) / 8)));
-            chunk0 = chunk = (((p.batch_n + nc - 1) / nc) + 7) & ~7; n_chunks = (p.batch_n + chunk - 1) / chunk;
+            const int nc = static_cast<int>(std::min<u64>(want, static_cast<u64>(n8)));
+            chunk = (((p.batch_n + nc - 1) / nc) + 7) & ~7; n_chunks = (p.batch_n + chunk - 1) / chunk;
         } else {
-            // k tail chunks of 8 samples: their work (8 k frames over the whole image) must outlast the big chunk's last items
-            // (batch_n - 8 k samples of ONE pixel, ~80 us each at depth 50 on the default scene): with rho = item time per
-            // sample / image time per sample ~ 127000 / n_pix, k >= batch_n rho / (8 (1 + rho)).  From ~6 Mpixel up the tail is
-            // under 2 % of the launch and the batch stays one chunk.
-            const double rho = 127000.0 / static_cast<double>(n_pix);
-            int k = rho < 0.02 ? 0 : static_cast<int>(std::ceil(p.batch_n * rho / (8.0 * (1.0 + rho))));
-            const int n8 = (p.batch_n + 7) / 8;                 // 8-sample groups that hold samples
-            k = std::min(std::min(k, 4), n8 - 1);
-            chunk = 8; chunk0 = 8 * (n8 - k); n_chunks = 1 + k;
+            // a ladder of halving chunks, e.g. 64 frames = 32 + 16 + 8 + 8: the frames still queued behind a chunk take the whole image
+            // as long as that chunk's heaviest item takes one lane (a glass pixel: ~0.4 ms per sample; the image: n_pix x 0.63 ns per
+            // sample, i.e. more from ~0.6 Mpixel up), so the machine stays full while long items finish and the final tail is 8 samples
+            int g[9], n = 0, left = n8;
+            while (left > 1 && n < 7) { const int take = (left + 1) / 2; g[n++] = take; left -= take; }
+            if (left > 0) g[n++] = left;
+            p.n_ladder = n; n_chunks = n;
+            p.ladder[0] = 0;
+            for (int i = 0; i < n; ++i) p.ladder[i + 1] = p.ladder[i] + 8 * g[i];
         }
-        p.chunk0_spp = chunk0; p.chunk_spp = chunk; p.n_chunks = n_chunks;
+        p.chunk_spp = chunk; p.n_chunks = n_chunks;
         p.partial = nullptr;
         if (n_chunks > 1) { if (int r = ensure_partial(c, n_pix, n_chunks - 1)) return r; p.partial = c->partial; }
         void* args[] = {&p};

@@ -45,8 +45,9 @@ struct RenderParams {
     uint16_t* hits;              // [W*H][hit_stride]: slot + 1 of the sphere the primary ray of (pixel, batch sample) hits, 0 = sky
     int hit_stride;              // samples per row: batch_n rounded up to a multiple of 16 (rows are whole 32-byte sectors)
     int batch_s0, batch_n;
-    int chunk0_spp;              // stage 2: samples of chunk 0 of the batch (accumulated straight into hdr); chunks 1.. have chunk_spp samples
-                                 // each and go through partial[chunk - 1].  Both are multiples of 8 (record alignment)
+    int n_ladder;                // stage 2: > 0: chunk c of the batch covers samples [ladder[c], ladder[c + 1]) (halving sizes, see rt_b200.cu);
+    int ladder[10];              // 0: every chunk has chunk_spp samples.  Chunk 0 is accumulated straight into hdr, chunk c >= 1 goes through
+                                 // partial[c - 1].  All boundaries are multiples of 8 (record alignment)
     int overwrite;               // 1: this launch starts the running sum (no read of hdr): RT_FLAG_OVERWRITE, first batch of the call
 };
 
@@ -484,8 +485,8 @@ __global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : RT_MAX
                     else if (item_to_pixel(p, item, chunk, px, py)) {
                         pix = py * p.W + px;
                         // chunk 0 continues the pixel's running sum in place; later chunks start partial sums (multiples of 8: records stay aligned)
-                        s_cur = chunk == 0 ? 0 : p.chunk0_spp + (chunk - 1) * p.chunk_spp;
-                        s_end = min(p.batch_n, s_cur + (chunk == 0 ? p.chunk0_spp : p.chunk_spp));
+                        if (p.n_ladder) { s_cur = p.ladder[chunk]; s_end = min(p.batch_n, p.ladder[chunk + 1]); }
+                        else { s_cur = chunk * p.chunk_spp; s_end = min(p.batch_n, s_cur + p.chunk_spp); }
                         acc = (chunk == 0 && !p.overwrite) ? p.hdr[pix] : make_float4(0.f, 0.f, 0.f, 0.f);
                         st = PS_SCAN;
                     }
