@@ -41,8 +41,8 @@ for want, title in (("rt_path_kernelILi0ELb0ELi5ELb0", "rt_path_kernel<MODE_CULL
     ins = kernels[name]
     pat = "".join(cls(op) for _, op in ins)
     best = max(re.finditer(r"[FSL]{1}[FSLo]{60,}?(?=o{3,}|$)", pat), key=lambda m: m.group(0).count("F"))
-    a = best.start(); b = a + len(best.group(0).rstrip("o"))
-    while a > 0 and pat[a - 1] == "L":
+    a = best.start() + best.group(0).index("F"); b = best.start() + len(best.group(0).rstrip("o"))
+    while a > 0 and pat[a - 1] == "L":                       # the loads that feed the first FMAs
         a -= 1
     body = ins[a:b]
     c = collections.Counter(cls(op) for _, op in body)
