@@ -171,7 +171,8 @@ def test_bench_traffic_lookup_and_reference_arm_shape():
     table = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
     for key in ("c3:brute", "c3:accel"):
         wl, q = key.split(":")
-        assert bench._ncu_traffic(wl, q) == table[key]["bytes"] == table[key]["read"] + table[key]["write"]
+        assert bench._ncu_traffic(wl, q) == table[key]["bytes"] == sum(k["bytes"] for k in table[key]["per_kernel"].values())
+        assert table[key]["bytes"] < 2.5 * table[key]["algorithmic_bytes"]        # traffic well above the algorithmic bytes = wasted re-reads
     assert bench._ncu_traffic("c4", "brute") is None
     assert bench._ncu_traffic("nope", "brute") is None
 
