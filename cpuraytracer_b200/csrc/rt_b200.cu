@@ -909,6 +909,9 @@ static int render_one_kernel(rt_context* c, rt::RenderParams& p, int spp, uint32
     return RT_OK;
 }
 
+#ifndef RT_LADDER_GRAN
+#define RT_LADDER_GRAN 8
+#endif
 // Two-stage schedule (default): per batch of frames one first-hit launch, then one path launch per light.
 static int render_two_stage(rt_context* c, rt::RenderParams& p, int spp, int max_depth, uint32_t flags) {
     const size_t n_pix = static_cast<size_t>(c->W) * c->H;
@@ -954,12 +957,14 @@ static int render_two_stage(rt_context* c, rt::RenderParams& p, int spp, int max
             // a ladder of halving chunks, e.g. 64 frames = 32 + 16 + 8 + 8: the frames still queued behind a chunk take the whole image
             // as long as that chunk's heaviest item takes one lane (a glass pixel: ~0.4 ms per sample; the image: n_pix x 0.63 ns per
             // sample, i.e. more from ~0.6 Mpixel up), so the machine stays full while long items finish and the final tail is 8 samples
-            int g[9], n = 0, left = n8;
+            // RT_LADDER_GRAN: frames per rung unit.  8 = finest (tail of 8 frames; the last two rungs share a 32-byte record sector);
+            // 16 = a record sector belongs to exactly one work item (64 frames = 32 + 16 + 16, one partial buffer less).
+            int g[9], n = 0, left = (p.batch_n + RT_LADDER_GRAN - 1) / RT_LADDER_GRAN;
             while (left > 1 && n < 7) { const int take = (left + 1) / 2; g[n++] = take; left -= take; }
             if (left > 0) g[n++] = left;
             p.n_ladder = n; n_chunks = n;
             p.ladder[0] = 0;
-            for (int i = 0; i < n; ++i) p.ladder[i + 1] = p.ladder[i] + 8 * g[i];
+            for (int i = 0; i < n; ++i) p.ladder[i + 1] = p.ladder[i] + RT_LADDER_GRAN * g[i];
         }
         p.chunk_spp = chunk; p.n_chunks = n_chunks;
         p.partial = nullptr;

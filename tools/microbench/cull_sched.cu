@@ -51,6 +51,34 @@ template <bool SH, int DELAY, int AHEAD> __global__ void __launch_bounds__(896) 
     }
     out[blockIdx.x * blockDim.x + threadIdx.x] = acc;
 }
+// R independent closest-only rays per lane share each loaded sphere pair (stage 1 with R frames of a pixel per lane)
+template <int R> __global__ void __launch_bounds__(896) k_r(const CullRay* rays, const float4* g, int np, int iters, uint32_t* out) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    float4* sA = reinterpret_cast<float4*>(smem); float4* sB = sA + np;
+    for (int i = threadIdx.x; i < np * 5 / 2; i += blockDim.x) sA[i] = g[i];
+    __syncthreads();
+    CullRay r[R];
+#pragma unroll
+    for (int j = 0; j < R; ++j) { r[j] = rays[blockIdx.x * blockDim.x + threadIdx.x]; r[j].od += 0.37f * j; r[j].ndx -= 0.11f * j; }
+    uint32_t acc = 0;
+    for (int it = 0; it < iters; ++it) {
+        for (int gi = 0; gi < np / 16; ++gi) {
+            uint32_t mc[R];
+#pragma unroll
+            for (int j = 0; j < R; ++j) mc[j] = 0;
+#pragma unroll
+            for (int q = 0; q < 16; ++q) {
+                const float4 A = sA[gi * 16 + q], B = sB[gi * 16 + q];
+#pragma unroll
+                for (int j = 0; j < R; ++j) { u64 d1, d2; fma_part<false>(r[j], A, B, make_float2(0.f, 0.f), d1, d2); SHIFT2(mc[j], d1); }
+            }
+#pragma unroll
+            for (int j = 0; j < R; ++j) acc += (j + 1) * __popc(~mc[j]);
+        }
+        r[0].noo += 1e-7f * static_cast<float>(acc & 1u);
+    }
+    out[blockIdx.x * blockDim.x + threadIdx.x] = acc;
+}
 template <class F> float timeit(F f) { cudaEvent_t a, b; cudaEventCreate(&a); cudaEventCreate(&b); f(); cudaDeviceSynchronize(); cudaEventRecord(a); f(); cudaEventRecord(b); cudaEventSynchronize(b); float ms; cudaEventElapsedTime(&ms, a, b); return ms; }
 int main() {
     cudaDeviceProp p; cudaGetDeviceProperties(&p, 0);
@@ -67,5 +95,10 @@ int main() {
         printf("%s delay %d ahead %d: %8.3f ms  %6.2f clk per pair per SMSP @%d MHz %s\n", SH ? "CS" : "C ", D, A, ms, ms * 1e-3 * p.clockRate * 1e3 / (pairs / (sms * 4)), p.clockRate / 1000, e ? cudaGetErrorString(e) : ""); }
     RUN(true, 0, 0) RUN(true, 1, 0) RUN(true, 2, 0) RUN(true, 0, 1) RUN(true, 1, 1) RUN(true, 2, 1) RUN(true, 1, 2) RUN(true, 2, 2) RUN(true, 4, 2)
     RUN(false, 0, 0) RUN(false, 1, 0) RUN(false, 2, 0) RUN(false, 1, 1) RUN(false, 2, 1) RUN(false, 2, 2) RUN(false, 4, 2)
+#define RUNR(R) { cudaFuncSetAttribute(k_r<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+        const float ms = timeit([&] { k_r<R><<<grid, tpb, smem>>>(rays, g, np, iters, out); }); const cudaError_t e = cudaGetLastError(); \
+        const double pairs = (double)grid * tpb / 32.0 * iters * np * R;   /* warp-level pair evaluations per ray */ \
+        printf("C  %d rays per lane: %8.3f ms  %6.2f clk per pair and ray per SMSP %s\n", R, ms, ms * 1e-3 * p.clockRate * 1e3 / (pairs / (sms * 4)), e ? cudaGetErrorString(e) : ""); }
+    RUNR(1) RUNR(2) RUNR(3) RUNR(4)
     return 0;
 }
