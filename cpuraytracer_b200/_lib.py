@@ -21,6 +21,7 @@ RT_MAT_OPAQUE, RT_MAT_METAL, RT_MAT_TRANSPARENT, RT_MAT_SKY = 0, 1, 2, 3
 RT_TEX_CONST, RT_TEX_CHECKER = 0, 1
 RT_FLAG_JITTER_OFF, RT_FLAG_LENS_OFF, RT_FLAG_WAVEFRONT, RT_FLAG_ACCEL, RT_FLAG_HALTON, RT_FLAG_DEBUG_NO_CULL = 1, 2, 4, 8, 16, 0x100
 RT_FLAG_OVERWRITE, RT_FLAG_DEBUG_ONE_KERNEL = 32, 0x200
+RT_STATIC_SCRATCH_BYTES, RT_STATIC_BATCH = 64 << 20, 16
 
 # flat scene description v1 (byte-identical to the structs in include/rt_b200.h)
 SPHERE_DTYPE = np.dtype([("cx", "<f4"), ("cy", "<f4"), ("cz", "<f4"), ("radius", "<f4"), ("material", "<i4")])
@@ -96,6 +97,8 @@ SYMBOLS = [
     ("rt_framebuffer_resize", C.c_int, [_P, C.c_int, C.c_int]),
     ("rt_framebuffer_clear", C.c_int, [_P]),
     ("rt_render", C.c_int, [_P, C.c_uint64, C.c_int, C.c_int, C.c_uint32]),
+    ("rt_render_static", C.c_int, [_P, C.c_uint64, C.c_int, C.c_int, C.c_uint32]),
+    ("rt_render_static_scratch_bytes", C.c_size_t, [C.c_int, C.c_int, C.c_int]),
     ("rt_read_hdr_sum", C.c_int, [_P, _P, C.c_size_t]),
     ("rt_write_hdr_sum", C.c_int, [_P, _P, C.c_size_t]),
     ("rt_resolve_ldr", C.c_int, [_P, C.c_uint64, _P, C.c_size_t]),

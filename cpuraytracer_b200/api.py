@@ -302,6 +302,13 @@ class Renderer:
         L.check(self._lib.rt_render(self._h, first, spp, max_depth, flags))
         self.sample_count += spp
 
+    def render_static(self, spp: int, max_depth: int = 50, flags: int = 0, first_sample: Optional[int] = None) -> None:
+        """rt_render_static: the same render with its scratch in the library's static device array -- allocates nothing
+        (include/rt_b200.h has the limit and the sharing rule; no counterpart in the reference)."""
+        first = self.sample_count + 1 if first_sample is None else first_sample
+        L.check(self._lib.rt_render_static(self._h, first, spp, max_depth, flags))
+        self.sample_count += spp
+
     def synchronize(self) -> None:
         L.check(self._lib.rt_synchronize(self._h))
 

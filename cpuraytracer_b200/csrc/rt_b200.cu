@@ -1022,6 +1022,97 @@ int rt_render(rt_context* c, uint64_t first_sample, int spp, int max_depth, uint
     return RT_OK;
 }
 
+// ------------------------------------------------------------------------------------------------
+// rt_render_static: the two-stage render with ALL of its scratch memory (per-call Halton tables, first-hit records) in a
+// file-scope device array instead of cudaMalloc'ed buffers.  No counterpart in the reference; added
+// for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+// The array is held by every GPU that loads the library until the process exits.  Every call on a device shares it and it keeps
+// the last call's contents: nothing in it has to start at zero (the tables and the records of every pixel / frame the path stage
+// reads are rewritten by this call's own table and first-hit launches first), but two calls whose kernels overlap on the GPU
+// (different streams / contexts on one device) race on it.
+// ------------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_static_scratch[RT_STATIC_SCRATCH_BYTES];
+static unsigned char* g_static_scratch_ptr[64];          // per device: the array's DEVICE address (the symbol itself is a host-side stand-in)
+static int static_scratch_of_current_device(int device, unsigned char** out) {
+    if (device < 0 || device >= 64) return fail(RT_ERR_UNSUPPORTED, "rt_render_static: device %d out of the supported range [0,64)", device);
+    if (!g_static_scratch_ptr[device]) {                 // once per device, with that device current (ctx_use ran)
+        void* ptr = nullptr;
+        RT_CUDA(cudaGetSymbolAddress(&ptr, g_static_scratch));
+        if (!ptr) return fail(RT_ERR_CUDA, "rt_render_static: cudaGetSymbolAddress returned a null address");
+        g_static_scratch_ptr[device] = static_cast<unsigned char*>(ptr);
+    }
+    *out = g_static_scratch_ptr[device];
+    return RT_OK;
+}
+size_t rt_render_static_scratch_bytes(int width, int height, int spp) {
+    if (width <= 0 || height <= 0 || spp < 0) return 0;
+    auto a256 = [](size_t x) { return (x + 255u) & ~static_cast<size_t>(255u); };
+    const size_t n_pix = static_cast<size_t>(width) * height;
+    return a256(static_cast<size_t>(spp) * sizeof(float2)) + a256((static_cast<size_t>(spp) + width + height) * sizeof(float2))
+         + n_pix * RT_STATIC_BATCH * sizeof(uint16_t);
+}
+int rt_render_static(rt_context* c, uint64_t first_sample, int spp, int max_depth, uint32_t flags) {
+    if (!c) return fail(RT_ERR_INVALID_ARGUMENT, "rt_render_static: ctx is NULL");
+    if (!c->scene_set || !c->camera_set || !c->hdr()) return fail(RT_ERR_NOT_READY, "rt_render_static: scene, camera and framebuffer must be set first");
+    if (first_sample < 1 || spp < 0 || max_depth < 0) return fail(RT_ERR_INVALID_ARGUMENT, "rt_render_static: first_sample >= 1, spp >= 0, max_depth >= 0 required");
+    if (flags & ~(RT_FLAG_JITTER_OFF | RT_FLAG_LENS_OFF | RT_FLAG_ACCEL | RT_FLAG_OVERWRITE))
+        return fail(RT_ERR_INVALID_ARGUMENT, "rt_render_static: only RT_FLAG_JITTER_OFF, RT_FLAG_LENS_OFF, RT_FLAG_ACCEL and RT_FLAG_OVERWRITE are supported (flags 0x%x)", flags);
+    if ((flags & RT_FLAG_ACCEL) && !c->accel_ok) return fail(RT_ERR_UNSUPPORTED, "rt_render_static: RT_FLAG_ACCEL unavailable for this scene: %s", c->accel_why.c_str());
+    if (c->global_scene && !(flags & RT_FLAG_ACCEL)) return fail(RT_ERR_UNSUPPORTED, "rt_render_static: %d spheres do not fit in shared memory; use rt_render", c->n_spheres);
+    const size_t need = rt_render_static_scratch_bytes(c->W, c->H, spp);
+    if (need > static_cast<size_t>(RT_STATIC_SCRATCH_BYTES))
+        return fail(RT_ERR_UNSUPPORTED, "rt_render_static: %dx%d with %d spp needs %zu B of scratch, the static array holds %zu B "
+                    "(32 B per pixel + 16 B per frame + 8 B per column and row); use rt_render, or fewer frames per call", c->W, c->H, spp, need,
+                    static_cast<size_t>(RT_STATIC_SCRATCH_BYTES));
+    if (spp == 0) return RT_OK;
+    if (int r = ctx_use(c)) return r;
+    unsigned char* scratch = nullptr;
+    if (int r = static_scratch_of_current_device(c->device, &scratch)) return r;
+    auto a256 = [](size_t x) { return (x + 255u) & ~static_cast<size_t>(255u); };
+    const size_t n_pix = static_cast<size_t>(c->W) * c->H;
+    const size_t n_lens = static_cast<size_t>(spp) + c->W + c->H;
+    float2* jitter = reinterpret_cast<float2*>(scratch);
+    float2* lens = reinterpret_cast<float2*>(scratch + a256(static_cast<size_t>(spp) * sizeof(float2)));
+    uint16_t* hits = reinterpret_cast<uint16_t*>(reinterpret_cast<unsigned char*>(lens) + a256(n_lens * sizeof(float2)));
+    // launch parameters: as prepare_frames + render_two_stage build them, with the scratch pointers above, batches of RT_STATIC_BATCH
+    // frames and ONE work item per pixel and batch (sequential per-pixel sums, the reference's order; no partial buffers)
+    rt::RenderParams p = c->base;
+    p.W = c->W; p.H = c->H; p.tiles_x = (c->W + 7) / 8; p.tiles_y = (c->H + 3) / 4;
+    p.first_sample = first_sample; p.spp = spp; p.max_depth = max_depth; p.flags = flags; p.seed = c->seed;
+    p.exposure = static_cast<float>(std::pow(2, c->exposure_stops));
+    p.hdr = c->hdr(); p.work_counter = c->counters; p.stats = c->counters + 1;
+    p.jitter = jitter; p.lens = lens; p.hits = hits; p.partial = nullptr;
+    rt::rt_tables_kernel<<<static_cast<unsigned>((n_lens + 255) / 256), 256, 0, c->stream>>>(first_sample, spp, static_cast<int>(n_lens), jitter, lens);
+    ++c->launches;
+    const bool accel = (flags & RT_FLAG_ACCEL) != 0;
+    const int mode = accel ? rt::MODE_ACCEL : rt::MODE_CULL;
+    const int gshift = accel ? p.accel.gshift : 5;
+    const int tpb = accel ? c->accel_tpb : c->path_tpb, bps = accel ? c->accel_bps : c->path_bps;
+    const size_t smem = accel ? accel_cta_smem_bytes(p.accel, tpb) : cta_smem_bytes(c->n_pad, tpb, false);
+    const int grid = c->prop.multiProcessorCount * bps;
+    const void* k_first = first_hit_kernel(mode, gshift);
+    const void* k_path = path_kernel(mode, false, gshift, max_depth == 0);
+    const int n_launch_lights = 1 + static_cast<int>(c->extra_lights.size());
+    const rt::RenderParams base = p;
+    for (int s0 = 0; s0 < spp; s0 += RT_STATIC_BATCH) {
+        p = base;
+        p.batch_s0 = s0; p.batch_n = std::min<int>(RT_STATIC_BATCH, spp - s0); p.hit_stride = RT_STATIC_BATCH;
+        p.n_ladder = 0; p.chunk_spp = RT_STATIC_BATCH; p.n_chunks = 1;
+        void* args[] = {&p};
+        RT_CUDA(cudaLaunchKernel(k_first, dim3(grid), dim3(tpb), args, smem, c->stream));
+        ++c->launches;
+        for (int k = 0; k < n_launch_lights; ++k) {
+            if (k > 0) select_extra_light(c, k, p);
+            p.overwrite = ((flags & RT_FLAG_OVERWRITE) && s0 == 0 && k == 0) ? 1 : 0;
+            RT_CUDA(cudaMemsetAsync(c->counters, 0, sizeof(u64), c->stream));
+            RT_CUDA(cudaLaunchKernel(k_path, dim3(grid), dim3(tpb), args, smem, c->stream));
+            ++c->launches;
+        }
+    }
+    RT_CUDA(cudaGetLastError());
+    return RT_OK;
+}
+
 int rt_read_hdr_sum(rt_context* c, float* rgba, size_t n_pixels) {
     if (!c || !rgba) return fail(RT_ERR_INVALID_ARGUMENT, "rt_read_hdr_sum: NULL argument");
     if (!c->hdr()) return fail(RT_ERR_NOT_READY, "rt_read_hdr_sum: no framebuffer");

@@ -154,6 +154,25 @@ RT_API int  rt_framebuffer_clear(rt_context* ctx);
  * m_sampleCount == first_sample (>= 1), with AppSettings::k_recursionDepth == max_depth.
  * Adds to the running sum; asynchronous on the context's stream. */
 RT_API int  rt_render(rt_context* ctx, uint64_t first_sample, int spp, int max_depth, uint32_t flags);
+/* rt_render_static -- NO COUNTERPART IN THE REFERENCE; added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same contract and same result as
+ * rt_render on its default two-stage schedule (flags: RT_FLAG_JITTER_OFF, RT_FLAG_LENS_OFF, RT_FLAG_ACCEL, RT_FLAG_OVERWRITE only;
+ * counter RNG; any number of lights), but the call allocates NOTHING: its scratch memory -- the per-call Halton tables and the
+ * first-hit records the path kernel regenerates from -- lives in a file-scope `static __device__` array of RT_STATIC_SCRATCH_BYTES
+ * (64 MiB, held by every GPU that loads the library until the process exits) whose device address the library takes once per
+ * device with cudaGetSymbolAddress.  Frames are rendered in batches of RT_STATIC_BATCH (16), one work item per pixel and batch
+ * (sequential per-pixel sums).  Inputs (scene, camera) and the output (the running-sum framebuffer) are the context's, set up
+ * beforehand with the calls above; rt_render_static itself calls no cudaMalloc / cudaFree / cudaEventCreate and records no timing
+ * events (rt_stats.render_ms does not include it).
+ * LIMIT: rt_render_static_scratch_bytes(W, H, spp) = 32 B per pixel + 16 B per frame + 8 B per column and row (each table rounded
+ * up to 256 B) must be <= RT_STATIC_SCRATCH_BYTES -- e.g. 1920x1080 with up to 47,000 frames per call, not 3840x2160 -- else
+ * RT_ERR_UNSUPPORTED with the figures in rt_last_error().
+ * SHARING: every call on a device uses the same array, which keeps the last call's contents; nothing in it needs clearing (each
+ * call rewrites what it reads), but calls whose kernels OVERLAP on one GPU (two contexts / streams) race on it: serialise them. */
+#define RT_STATIC_SCRATCH_BYTES (64u << 20)
+#define RT_STATIC_BATCH 16
+RT_API int    rt_render_static(rt_context* ctx, uint64_t first_sample, int spp, int max_depth, uint32_t flags);
+RT_API size_t rt_render_static_scratch_bytes(int width, int height, int spp);   /* host only; 0 for invalid arguments */
 /* m_backbufferHdr (app.h:26): float4 per pixel, row-major j*W+i, row 0 = top; xyz = sum of exposure-scaled
  * samples, w = number of samples accumulated. */
 RT_API int  rt_read_hdr_sum(rt_context* ctx, float* rgba, size_t n_pixels);
