@@ -255,6 +255,7 @@ struct rt_context {
     float4* partial = nullptr; size_t partial_bytes = 0;
     uint16_t* hits = nullptr; size_t hits_bytes = 0;   // first-hit records of one batch (two-stage schedule)
     int path_tpb = 0, path_bps = 0;                    // CTA size / resident CTAs per SM of the stage-2 kernel
+    int first_tpb = 0, first_bps = 0;                  // CTA size / resident CTAs per SM of the brute-force stage-1 kernel (its own register budget)
     bool global_scene = false;                         // the sphere list does not fit one CTA's shared memory: kernels read it from global memory
     int accel_gshift_min = 3;                          // finest group size rt_set_scene tries (rt_set_accel_group_slots)
     float2 *jitter = nullptr, *lens = nullptr; size_t jitter_cap = 0, lens_cap = 0;
@@ -736,6 +737,15 @@ int rt_set_scene(rt_context* c, const rt_scene* s) {
         if (bps * tpb > c->path_bps * c->path_tpb) { c->path_tpb = tpb; c->path_bps = bps; }
     }
     if (c->global_scene) { best_tpb = c->path_tpb; best_bps = c->path_bps; }
+    c->first_tpb = 0; c->first_bps = 0;
+    for (int tpb = 128; tpb <= std::min(RT_MAX_TPB, RT_FIRST_RAYS == 1 ? RT_MAX_TPB : RT_FIRST_MAX_TPB); tpb += 128) {
+        const size_t smem = cta_smem_bytes(n_pad, tpb, c->global_scene);
+        if (smem > static_cast<size_t>(optin)) break;
+        int bps = 0;
+        RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, first_hit_kernel(scene_mode, 5), tpb, smem));
+        if (bps * tpb > c->first_bps * c->first_tpb) { c->first_tpb = tpb; c->first_bps = bps; }
+    }
+    if (c->first_bps < 1) return fail(RT_ERR_UNSUPPORTED, "rt_set_scene: first-hit kernel does not fit on an SM with %zu B shared memory", cta_smem_bytes(n_pad, 128, c->global_scene));
     if (c->path_bps < 1) return fail(RT_ERR_UNSUPPORTED, "rt_set_scene: path kernel does not fit on an SM with %zu B shared memory", cta_smem_bytes(n_pad, 256));
     if (best_bps < 1) return fail(RT_ERR_UNSUPPORTED, "rt_set_scene: render kernel does not fit on an SM with %zu B shared memory", cta_smem_bytes(n_pad, 256));
     c->tpb = best_tpb;
@@ -924,6 +934,10 @@ static int render_two_stage(rt_context* c, rt::RenderParams& p, int spp, int max
     const int grid = c->prop.multiProcessorCount * bps;
     const void* k_first = first_hit_kernel(mode, gshift);
     const void* k_path = path_kernel(mode, halton, gshift, direct);
+    // stage 1 of the brute-force query runs several rays per lane with its own register budget, hence its own CTA shape
+    const bool own1 = mode == rt::MODE_CULL || mode == rt::MODE_CULL_GLOBAL;
+    const int tpb1 = own1 ? c->first_tpb : tpb, grid1 = own1 ? c->prop.multiProcessorCount * c->first_bps : grid;
+    const size_t smem1 = own1 ? cta_smem_bytes(c->n_pad, tpb1, c->global_scene) : smem;
     // batch: as many frames as fit first-hit records of max(256 MiB, two running-sum buffers) (2 B per pixel and frame), a
     // multiple of 16, at most 4096: 64 frames at 1920x1080, 16 at 3840x2160 -- the records are the only per-batch allocation
     const size_t cap_bytes = std::max<size_t>(256ull << 20, n_pix * 32);
@@ -970,7 +984,7 @@ static int render_two_stage(rt_context* c, rt::RenderParams& p, int spp, int max
         p.partial = nullptr;
         if (n_chunks > 1) { if (int r = ensure_partial(c, n_pix, n_chunks - 1)) return r; p.partial = c->partial; }
         void* args[] = {&p};
-        RT_CUDA(cudaLaunchKernel(k_first, dim3(grid), dim3(tpb), args, smem, c->stream));
+        RT_CUDA(cudaLaunchKernel(k_first, dim3(grid1), dim3(tpb1), args, smem1, c->stream));
         ++c->launches;
         // RT_FLAG_HALTON with several lights: the reference draws once per vertex and loops over the lights there (material.cpp:4-13);
         // here light k re-walks the batch's paths, so the materials' indices are rewound to where light 0's pass found them and
@@ -1092,6 +1106,8 @@ int rt_render_static(rt_context* c, uint64_t first_sample, int spp, int max_dept
     const int grid = c->prop.multiProcessorCount * bps;
     const void* k_first = first_hit_kernel(mode, gshift);
     const void* k_path = path_kernel(mode, false, gshift, max_depth == 0);
+    const int tpb1 = accel ? tpb : c->first_tpb, grid1 = accel ? grid : c->prop.multiProcessorCount * c->first_bps;
+    const size_t smem1 = accel ? smem : cta_smem_bytes(c->n_pad, tpb1, false);
     const int n_launch_lights = 1 + static_cast<int>(c->extra_lights.size());
     const rt::RenderParams base = p;
     for (int s0 = 0; s0 < spp; s0 += RT_STATIC_BATCH) {
@@ -1099,7 +1115,7 @@ int rt_render_static(rt_context* c, uint64_t first_sample, int spp, int max_dept
         p.batch_s0 = s0; p.batch_n = std::min<int>(RT_STATIC_BATCH, spp - s0); p.hit_stride = RT_STATIC_BATCH;
         p.n_ladder = 0; p.chunk_spp = RT_STATIC_BATCH; p.n_chunks = 1;
         void* args[] = {&p};
-        RT_CUDA(cudaLaunchKernel(k_first, dim3(grid), dim3(tpb), args, smem, c->stream));
+        RT_CUDA(cudaLaunchKernel(k_first, dim3(grid1), dim3(tpb1), args, smem1, c->stream));
         ++c->launches;
         for (int k = 0; k < n_launch_lights; ++k) {
             if (k > 0) select_extra_light(c, k, p);

@@ -372,9 +372,16 @@ __global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : RT_MAX
 // Arithmetic per path is unchanged (same device functions, same order), so the bits are those of the one-kernel schedule.
 // ------------------------------------------------------------------------------------------------------------------
 
+#ifndef RT_FIRST_RAYS
+#define RT_FIRST_RAYS 4    /* frames per lane and query of the brute-force first-hit stage (1, 2 or 4) */
+#endif
 // Stage 1.  Work item of a WARP = (8x4 pixel tile, group of 16 consecutive batch samples); static round-robin over the grid.
+#ifndef RT_FIRST_MAX_TPB
+#define RT_FIRST_MAX_TPB 512   /* brute-force first-hit stage with RT_FIRST_RAYS rays per lane: up to 128 registers per thread */
+#endif
 template <int MODE, int GSHIFT = 5>
-__global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : RT_MAX_TPB) rt_first_hit_kernel(const RenderParams p) {
+__global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : (MODE == MODE_NO_CULL || RT_FIRST_RAYS == 1) ? RT_MAX_TPB : RT_FIRST_MAX_TPB)
+rt_first_hit_kernel(const RenderParams p) {
     extern __shared__ __align__(256) unsigned char smem[];
     float4 *sA = nullptr, *sB = nullptr; float2* sC = nullptr; float* sR = nullptr; uint32_t* lists = nullptr;
     AccelSmem av{};
@@ -395,27 +402,39 @@ __global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : RT_MAX
         const int py = static_cast<int>((tile / p.tiles_x) * 4u + (lane >> 3));
         const bool valid = px < p.W && py < p.H;
         u64 rec0 = 0ull, rec1 = 0ull, rec2 = 0ull, rec3 = 0ull;      // 16 records of this lane's pixel = one 32-byte sector
+        // R frames of the pixel per query: the brute-force cull shares every sphere-pair load between R rays (closest_query_multi)
+        constexpr int R = (MODE == MODE_CULL || MODE == MODE_CULL_GLOBAL) ? RT_FIRST_RAYS : 1;
 #pragma unroll 1
-        for (int k = 0; k < 16; ++k) {
-            const int sb = g * 16 + k;                       // sample index inside the batch
-            if (sb >= p.batch_n) break;                      // warp-uniform
-            const int s = p.batch_s0 + sb;                   // index into the per-call Halton tables
-            V3 o = mk3(0.f, 0.f, 0.f), d = mk3(0.f, 0.f, 1.f);
-            if (valid) {
-                float jx = 0.f, jy = 0.f, lx = 0.f, ly = 0.f;
-                if (!(p.flags & RT_FLAG_JITTER_OFF_)) { const float2 j = __ldg(&p.jitter[s]); jx = j.x; jy = j.y; }
-                if (!(p.flags & RT_FLAG_LENS_OFF_)) { const float2 l = __ldg(&p.lens[s + px + py]); lx = l.x; ly = l.y; }
-                const float u = div_rn(static_cast<float>(px) + jx, static_cast<float>(p.W));   // spheres-app.cpp:149
-                const float v = div_rn(static_cast<float>(py) + jy, static_cast<float>(p.H));   // :150
-                camera_get_ray(p.cam, u, v, lx, ly, o, d);
-                ++n_closest;
+        for (int k = 0; k < 16; k += R) {
+            if (g * 16 + k >= p.batch_n) break;              // warp-uniform
+            V3 o[R], d[R]; bool want[R]; QueryResult q[R];
+#pragma unroll
+            for (int j = 0; j < R; ++j) {
+                const int sb = g * 16 + k + j;               // sample index inside the batch
+                const int s = p.batch_s0 + sb;               // index into the per-call Halton tables
+                want[j] = valid && sb < p.batch_n;
+                o[j] = mk3(0.f, 0.f, 0.f); d[j] = mk3(0.f, 0.f, 1.f);
+                if (want[j]) {
+                    float jx = 0.f, jy = 0.f, lx = 0.f, ly = 0.f;
+                    if (!(p.flags & RT_FLAG_JITTER_OFF_)) { const float2 jj = __ldg(&p.jitter[s]); jx = jj.x; jy = jj.y; }
+                    if (!(p.flags & RT_FLAG_LENS_OFF_)) { const float2 l = __ldg(&p.lens[s + px + py]); lx = l.x; ly = l.y; }
+                    const float u = div_rn(static_cast<float>(px) + jx, static_cast<float>(p.W));   // spheres-app.cpp:149
+                    const float v = div_rn(static_cast<float>(py) + jy, static_cast<float>(p.H));   // :150
+                    camera_get_ray(p.cam, u, v, lx, ly, o[j], d[j]);
+                    ++n_closest;
+                }
+                if (sb < p.batch_n) ++n_pass;
             }
-            QueryResult q;
-            if constexpr (MODE == MODE_ACCEL) q = fused_query_accel<GSHIFT, RAYS_CLOSEST>(av, p.accel, static_cast<int>(blockDim.x), o, d, Ldir, mk3(p.iLx, p.iLy, p.iLz), valid, false, acnt);
-            else q = fused_query<MODE == MODE_NO_CULL, RAYS_CLOSEST>(sA, sB, sC, sR, lists, static_cast<int>(blockDim.x), p.n_groups, p.n_spheres, o, d, Ldir, valid, false);
-            ++n_pass;
-            const u64 v16 = ((valid && q.idx >= 0) ? static_cast<u64>(((MODE == MODE_ACCEL) ? q.slot : q.idx) + 1) : 0ull) << (16 * (k & 3));
-            if (k < 4) rec0 |= v16; else if (k < 8) rec1 |= v16; else if (k < 12) rec2 |= v16; else rec3 |= v16;
+            if constexpr (R == 1) {
+                if constexpr (MODE == MODE_ACCEL) q[0] = fused_query_accel<GSHIFT, RAYS_CLOSEST>(av, p.accel, static_cast<int>(blockDim.x), o[0], d[0], Ldir, mk3(p.iLx, p.iLy, p.iLz), want[0], false, acnt);
+                else q[0] = fused_query<MODE == MODE_NO_CULL, RAYS_CLOSEST>(sA, sB, sC, sR, lists, static_cast<int>(blockDim.x), p.n_groups, p.n_spheres, o[0], d[0], Ldir, want[0], false);
+            } else closest_query_multi<R>(sA, sB, sR, lists, static_cast<int>(blockDim.x), p.n_groups, p.n_spheres, o, d, want, q);
+#pragma unroll
+            for (int j = 0; j < R; ++j) {
+                const int kk = k + j;
+                const u64 v16 = ((want[j] && q[j].idx >= 0) ? static_cast<u64>(((MODE == MODE_ACCEL) ? q[j].slot : q[j].idx) + 1) : 0ull) << (16 * (kk & 3));
+                if (kk < 4) rec0 |= v16; else if (kk < 8) rec1 |= v16; else if (kk < 12) rec2 |= v16; else rec3 |= v16;
+            }
         }
         if (valid) {                                         // two 16-byte stores into one aligned 32-byte sector: no partial-sector write reaches HBM
             const size_t pix = static_cast<size_t>(py) * p.W + px;
