@@ -240,7 +240,7 @@ struct rt_context {
     cudaDeviceProp prop{};
     int clock_khz = 0;
     // scene
-    float4 *cullA = nullptr, *cullB = nullptr; float2* cullC = nullptr; float* radius = nullptr; rt::DevMat* mats = nullptr;
+    float4 *cullA = nullptr, *cullB = nullptr; rt::DevMat* mats = nullptr;
     float4* geom = nullptr;
     // wavefront layout (RT_FLAG_WAVEFRONT): SoA path state, allocated on first use
     rt::WfState wf{}; void* wf_block = nullptr; unsigned int* wf_live = nullptr; int wf_bps = 0;
@@ -269,8 +269,8 @@ struct rt_context {
     int render_blocks_per_sm = 0, tpb = 256;
     // RT_FLAG_ACCEL: shared-memory image of the box hierarchy (rt_bvh.cuh), built by rt_set_scene
     uint4* accel_blob = nullptr; bool accel_ok = false; std::string accel_why;
-    struct ExtraLight { float L[3], lc[3], iL[3]; float2* cullC; };
-    std::vector<ExtraLight> extra_lights; float2* extra_cullC = nullptr;   // lights 1.. (one additional launch each, see rt_render)
+    struct ExtraLight { float L[3], lc[3], iL[3], rot[9]; float4 *cullA, *cullB; };
+    std::vector<ExtraLight> extra_lights; float4* extra_pairs = nullptr;   // lights 1.. (one additional launch each, see rt_render)
     u64* sampler = nullptr; size_t n_sampler = 0;   // RT_FLAG_HALTON: per-material-instance Halton indices (material.h:34,50-51,67); second half = snapshot
     int accel_tpb = 0, accel_bps = 0;
 
@@ -311,7 +311,7 @@ template <class T> static int dev_realloc(T*& p, size_t n) {
     RT_CUDA(cudaMalloc(&p, n * sizeof(T)));
     return RT_OK;
 }
-static size_t scene_smem_bytes(int n_pad) { return static_cast<size_t>(n_pad / 2) * 40u + static_cast<size_t>(n_pad) * 4u; }
+static size_t scene_smem_bytes(int n_pad) { return static_cast<size_t>(n_pad / 2) * 32u + static_cast<size_t>(n_pad) * 16u; }   // pair arrays + world-space (c, r)
 // scene arrays + the per-thread candidate lists (2 lists x RT_LIST_CAP words), see stage_scene()
 static size_t cta_smem_bytes(int n_pad, int tpb, bool global_scene = false) {
     size_t b = (global_scene ? 0u : scene_smem_bytes(n_pad)) + static_cast<size_t>(tpb) * 2u * RT_LIST_CAP * 4u;
@@ -563,8 +563,8 @@ void rt_context_destroy(rt_context* c) {
     cudaStreamSynchronize(c->stream);
     ev_collect(c);
     for (auto& e : c->pool) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
-    cudaFree(c->geom); cudaFree(c->wf_block); cudaFree(c->wf_live); cudaFree(c->accel_blob); cudaFree(c->sampler); cudaFree(c->extra_cullC);
-    cudaFree(c->cullA); cudaFree(c->cullB); cudaFree(c->cullC); cudaFree(c->radius); cudaFree(c->mats);
+    cudaFree(c->geom); cudaFree(c->wf_block); cudaFree(c->wf_live); cudaFree(c->accel_blob); cudaFree(c->sampler); cudaFree(c->extra_pairs);
+    cudaFree(c->cullA); cudaFree(c->cullB); cudaFree(c->mats);
     cudaFree(c->hdr_own); cudaFree(c->ldr); cudaFree(c->ids); cudaFree(c->mids); cudaFree(c->partial); cudaFree(c->hits);
     cudaFree(c->jitter); cudaFree(c->lens); cudaFree(c->counters);
     if (c->own_stream) cudaStreamDestroy(c->stream);
@@ -619,27 +619,43 @@ int rt_set_scene(rt_context* c, const rt_scene* s) {
     host::V3 Ln{0.f, 0.f, 0.f};
     if (has_light) Ln = host::normalize3({s->lights[0].dir[0], s->lights[0].dir[1], s->lights[0].dir[2]});   // light.cpp:7
     const double L[3] = {Ln.x, Ln.y, Ln.z};
-    std::vector<float4> A(np), B(np); std::vector<float2> C(np); std::vector<float> R(n_pad, 0.f);
+    std::vector<float4> A(np), B(np);
     std::vector<rt::DevMat> M(std::max(n, 1));
-    const double K = static_cast<double>(RT_CULL_K);
-    auto sphere_terms = [&](int i, float& cx, float& cy, float& cz, float& wn, float& ncl) {
-        if (i >= n) { cx = cy = cz = 0.f; wn = RT_PAD_W; ncl = 0.f; return; }
-        const rt_sphere_desc& sp = s->spheres[i];
-        cx = sp.cx; cy = sp.cy; cz = sp.cz;
-        const double cc = static_cast<double>(sp.cx) * sp.cx + static_cast<double>(sp.cy) * sp.cy + static_cast<double>(sp.cz) * sp.cz;
-        const double r2 = static_cast<double>(sp.radius) * sp.radius;
-        wn = static_cast<float>(r2 - cc + K * (cc + r2));            // -(|c|^2 - r^2) + slack
-        ncl = static_cast<float>(-(sp.cx * L[0] + sp.cy * L[1] + sp.cz * L[2]));
-        R[i] = sp.radius;
+    // Pair arrays of the cull in the light-aligned frame of light 0 (rt_device.cuh, SceneView): rows of `rot` = (e1, e2, L), c' = rot c,
+    // everything in double, one rounding to float per coordinate.  w = r^2 - |c|^2 + k (|c|^2 + r^2) is rotation invariant.
+    auto light_frame = [](const host::V3& Lu, bool lit, double rot[9]) {
+        if (!lit) { const double id[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1}; std::copy(id, id + 9, rot); return; }
+        double L[3] = {Lu.x, Lu.y, Lu.z};
+        const double ln = std::sqrt(L[0] * L[0] + L[1] * L[1] + L[2] * L[2]);
+        for (double& v : L) v /= ln;
+        const int ax = std::fabs(L[0]) <= std::fabs(L[1]) ? (std::fabs(L[0]) <= std::fabs(L[2]) ? 0 : 2) : (std::fabs(L[1]) <= std::fabs(L[2]) ? 1 : 2);
+        double u[3] = {0, 0, 0}; u[ax] = 1.0;                               // the axis least aligned with L
+        double e1[3] = {u[1] * L[2] - u[2] * L[1], u[2] * L[0] - u[0] * L[2], u[0] * L[1] - u[1] * L[0]};
+        const double n1 = std::sqrt(e1[0] * e1[0] + e1[1] * e1[1] + e1[2] * e1[2]);
+        for (double& v : e1) v /= n1;
+        const double e2[3] = {L[1] * e1[2] - L[2] * e1[1], L[2] * e1[0] - L[0] * e1[2], L[0] * e1[1] - L[1] * e1[0]};
+        for (int k = 0; k < 3; ++k) { rot[k] = e1[k]; rot[3 + k] = e2[k]; rot[6 + k] = L[k]; }
     };
-    for (int p = 0; p < np; ++p) {
-        float cx0, cy0, cz0, w0, l0, cx1, cy1, cz1, w1, l1;
-        sphere_terms(2 * p, cx0, cy0, cz0, w0, l0);
-        sphere_terms(2 * p + 1, cx1, cy1, cz1, w1, l1);
-        A[p] = make_float4(cx0, cx1, cy0, cy1);
-        B[p] = make_float4(cz0, cz1, w0, w1);
-        C[p] = make_float2(l0, l1);
-    }
+    auto fill_pairs = [&](const double rot[9], float4* Ao, float4* Bo) {
+        const double K = static_cast<double>(RT_CULL_K);
+        for (int p = 0; p < np; ++p) {
+            float v[2][4];
+            for (int h = 0; h < 2; ++h) {
+                const int i = 2 * p + h;
+                if (i >= n) { v[h][0] = v[h][1] = v[h][2] = 0.f; v[h][3] = RT_PAD_W; continue; }
+                const rt_sphere_desc& sp = s->spheres[i];
+                const double cw[3] = {sp.cx, sp.cy, sp.cz};
+                for (int k = 0; k < 3; ++k) v[h][k] = static_cast<float>(rot[3 * k] * cw[0] + rot[3 * k + 1] * cw[1] + rot[3 * k + 2] * cw[2]);
+                const double cc = cw[0] * cw[0] + cw[1] * cw[1] + cw[2] * cw[2], r2 = static_cast<double>(sp.radius) * sp.radius;
+                v[h][3] = static_cast<float>(r2 - cc + K * (cc + r2));      // -(|c|^2 - r^2) + slack
+            }
+            Ao[p] = make_float4(v[0][0], v[1][0], v[0][1], v[1][1]);
+            Bo[p] = make_float4(v[0][2], v[1][2], v[0][3], v[1][3]);
+        }
+    };
+    double rot0[9];
+    light_frame(Ln, has_light, rot0);
+    fill_pairs(rot0, A.data(), B.data());
     for (int i = 0; i < n; ++i) {
         const rt_material_desc& m = s->materials[s->spheres[i].material];
         rt::DevMat dm{}; dm.kind = m.kind; dm.smoothness = m.smoothness; dm.ior = m.ior; dm.mat_index = s->spheres[i].material;
@@ -652,24 +668,21 @@ int rt_set_scene(rt_context* c, const rt_scene* s) {
     }
     if (int r = dev_realloc(c->cullA, np)) return r;
     if (int r = dev_realloc(c->cullB, np)) return r;
-    if (int r = dev_realloc(c->cullC, np)) return r;
-    if (int r = dev_realloc(c->radius, n_pad)) return r;
     if (int r = dev_realloc(c->mats, M.size())) return r;
     c->n_sampler = 2 * std::max<size_t>(1, s->materials.size());
     if (int r = dev_realloc(c->sampler, 2 * c->n_sampler)) return r;    // [indices][snapshot taken before light 0's pass of a batch]
     RT_CUDA(cudaMemsetAsync(c->sampler, 0, 2 * c->n_sampler * sizeof(u64), c->stream));      // the reference's indices start at 0 with the scene
-    std::vector<float4> G(std::max(n, 1), make_float4(0.f, 0.f, 0.f, 1.f));
+    std::vector<float4> G(n_pad, make_float4(0.f, 0.f, 0.f, 1.f));            // padded: the kernels stage 2 * n_pairs_pad entries
     for (int i = 0; i < n; ++i) G[i] = make_float4(s->spheres[i].cx, s->spheres[i].cy, s->spheres[i].cz, s->spheres[i].radius);
     if (int r = dev_realloc(c->geom, G.size())) return r;
     RT_CUDA(cudaMemcpyAsync(c->geom, G.data(), G.size() * sizeof(float4), cudaMemcpyHostToDevice, c->stream));
     RT_CUDA(cudaMemcpyAsync(c->cullA, A.data(), np * sizeof(float4), cudaMemcpyHostToDevice, c->stream));
     RT_CUDA(cudaMemcpyAsync(c->cullB, B.data(), np * sizeof(float4), cudaMemcpyHostToDevice, c->stream));
-    RT_CUDA(cudaMemcpyAsync(c->cullC, C.data(), np * sizeof(float2), cudaMemcpyHostToDevice, c->stream));
-    RT_CUDA(cudaMemcpyAsync(c->radius, R.data(), n_pad * sizeof(float), cudaMemcpyHostToDevice, c->stream));
     RT_CUDA(cudaMemcpyAsync(c->mats, M.data(), M.size() * sizeof(rt::DevMat), cudaMemcpyHostToDevice, c->stream));
     RT_CUDA(cudaStreamSynchronize(c->stream));
     rt::RenderParams& b = c->base;
-    b.cullA = c->cullA; b.cullB = c->cullB; b.cullC = c->cullC; b.radius = c->radius; b.mats = c->mats; b.sphere_geom = c->geom;
+    b.cullA = c->cullA; b.cullB = c->cullB; b.mats = c->mats; b.sphere_geom = c->geom;
+    for (int k = 0; k < 9; ++k) b.rot[k] = static_cast<float>(rot0[k]);
     b.sampler = c->sampler;
     b.n_spheres = n; b.n_pairs_pad = np; b.n_groups = n_pad / 32; b.n_lights = has_light ? 1 : 0;
     b.Lx = b.Ly = b.Lz = 0.f; b.lcx = b.lcy = b.lcz = 0.f;
@@ -684,24 +697,22 @@ int rt_set_scene(rt_context* c, const rt_scene* s) {
     c->extra_lights.clear();
     if (s->lights.size() > 1) {
         const size_t ne = s->lights.size() - 1;
-        if (int r = dev_realloc(c->extra_cullC, ne * np)) return r;
-        std::vector<float2> CE(ne * np);
+        if (int r = dev_realloc(c->extra_pairs, 2 * ne * np)) return r;       // per further light: its own light-aligned pair arrays [A][B]
+        std::vector<float4> PE(2 * ne * np);
         for (size_t k = 1; k < s->lights.size(); ++k) {
             const rt_light_desc& l = s->lights[k];
             const host::V3 Lk = host::normalize3({l.dir[0], l.dir[1], l.dir[2]});
             rt_context::ExtraLight e{};
             e.L[0] = Lk.x; e.L[1] = Lk.y; e.L[2] = Lk.z;
             for (int q = 0; q < 3; ++q) e.lc[q] = l.luminance * l.color[q];
-            e.cullC = c->extra_cullC + (k - 1) * np;
-            for (int p = 0; p < np; ++p) {
-                float v[2] = {0.f, 0.f};
-                for (int h = 0; h < 2; ++h) { const int i = 2 * p + h; if (i < n) { const rt_sphere_desc& sp = s->spheres[i];
-                    v[h] = static_cast<float>(-(sp.cx * static_cast<double>(Lk.x) + sp.cy * static_cast<double>(Lk.y) + sp.cz * static_cast<double>(Lk.z))); } }
-                CE[(k - 1) * np + p] = make_float2(v[0], v[1]);
-            }
+            double rk[9];
+            light_frame(Lk, true, rk);
+            for (int q = 0; q < 9; ++q) e.rot[q] = static_cast<float>(rk[q]);
+            e.cullA = c->extra_pairs + 2 * (k - 1) * np; e.cullB = e.cullA + np;
+            fill_pairs(rk, PE.data() + 2 * (k - 1) * np, PE.data() + 2 * (k - 1) * np + np);
             c->extra_lights.push_back(e);
         }
-        RT_CUDA(cudaMemcpyAsync(c->extra_cullC, CE.data(), CE.size() * sizeof(float2), cudaMemcpyHostToDevice, c->stream));
+        RT_CUDA(cudaMemcpyAsync(c->extra_pairs, PE.data(), PE.size() * sizeof(float4), cudaMemcpyHostToDevice, c->stream));
         RT_CUDA(cudaStreamSynchronize(c->stream));
     }
     const rt_texture_desc& sky = s->textures[s->sky_texture];              // Emissive::Emit at uv = (0,0): material.cpp:172-175
@@ -870,7 +881,8 @@ static int render_wavefront(rt_context* c, const rt::RenderParams& p, uint32_t f
 static void select_extra_light(const rt_context* c, int k, rt::RenderParams& p) {
     const rt_context::ExtraLight& e = c->extra_lights[k - 1];
     p.Lx = e.L[0]; p.Ly = e.L[1]; p.Lz = e.L[2]; p.lcx = e.lc[0]; p.lcy = e.lc[1]; p.lcz = e.lc[2];
-    p.iLx = e.iL[0]; p.iLy = e.iL[1]; p.iLz = e.iL[2]; p.cullC = e.cullC;
+    p.iLx = e.iL[0]; p.iLy = e.iL[1]; p.iLz = e.iL[2]; p.cullA = e.cullA; p.cullB = e.cullB;
+    for (int q = 0; q < 9; ++q) p.rot[q] = e.rot[q];
     p.skyx = p.skyy = p.skyz = 0.f; p.primary_pass = 0;
 }
 static int ensure_partial(rt_context* c, size_t n_pix, int n_chunks) {

@@ -174,7 +174,7 @@ __device__ __forceinline__ QueryResult fused_query_accel(const AccelSmem& s, con
     cr.od = fmaf(o.x, d.x, fmaf(o.y, d.y, o.z * d.z));
     cr.oL = fmaf(o.x, L.x, fmaf(o.y, L.y, o.z * L.z));
     ExactCtx ex;
-    ex.sA = s.sA; ex.sB = s.sB; ex.sR = s.sR; ex.o = o; ex.d = d; ex.L = L;
+    ex.sA = s.sA; ex.sB = s.sB; ex.sR = s.sR; ex.G = nullptr; ex.o = o; ex.d = d; ex.L = L;
     ex.a = dot3(d, d);
     ex.aL = dot3(L, L);
     ex.ra = rcp_refined(ex.a); ex.raL = rcp_refined(ex.aL);

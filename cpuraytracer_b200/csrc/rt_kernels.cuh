@@ -14,9 +14,10 @@ namespace rt {
 
 struct RenderParams {
     // scene (global memory; the cull arrays are staged into shared memory by every CTA)
-    const float4* cullA; const float4* cullB; const float2* cullC; const float* radius;
+    const float4* cullA; const float4* cullB;   // pair arrays of the cull in the light-aligned frame of THIS launch's light (rt_device.cuh, SceneView)
+    float rot[9];                // that frame: rows e1, e2, L (identity without a light)
     const DevMat* mats;
-    const float4* sphere_geom;   // (cx, cy, cz, radius) per sphere, for kernels that do not stage the scene (wavefront shade)
+    const float4* sphere_geom;   // (cx, cy, cz, radius) per sphere (padded to n_pairs_pad * 2), world space: exact tests, hit records
     int n_spheres, n_pairs_pad, n_groups;
     int n_lights;
     float Lx, Ly, Lz;            // normalised light direction (light.cpp:7)
@@ -62,7 +63,7 @@ struct RenderParams {
 
 enum LaneState { ST_NEED_ITEM = 0, ST_NEW_PATH = 1, ST_IN_PATH = 2, ST_DONE = 3 };
 
-// Shared-memory layout of one CTA: [cullA np*16][cullB np*16][cullC np*8][radius 2np*4][candidate lists 2*CAP*blockDim*4].
+// Shared-memory layout of one CTA: [cullA np*16][cullB np*16][geom 2np*16][candidate lists 2*CAP*blockDim*4].
 // `lists` is this thread's column of the word-interleaved candidate lists (entry e at lists[e * blockDim.x]).
 #ifndef RT_MAX_TPB
 #define RT_MAX_TPB 896   /* launch bound of the brute-force kernels: 72 registers, no spills -> 7 CTAs x 128 threads = 28 warps per SM (r01t: +1 % over 768 / 80 registers) */
@@ -75,21 +76,32 @@ enum LaneState { ST_NEED_ITEM = 0, ST_NEW_PATH = 1, ST_IN_PATH = 2, ST_DONE = 3 
 // GLOBAL_SCENE (MODE_CULL_GLOBAL): a sphere list too large for one CTA's shared memory is read in place from global memory
 // (broadcast loads through L1 / L2; every lane of a warp reads the same address) and shared memory holds the candidate lists only.
 template <bool GLOBAL_SCENE = false>
-__device__ __forceinline__ void stage_scene(const RenderParams& p, float4*& sA, float4*& sB, float2*& sC, float*& sR, uint32_t*& lists, unsigned char* smem) {
+__device__ __forceinline__ SceneView stage_scene(const RenderParams& p, uint32_t*& lists, unsigned char* smem) {
     const int np = p.n_pairs_pad;
+    SceneView sv;
+    sv.rot = p.rot;
     if constexpr (GLOBAL_SCENE) {
-        sA = const_cast<float4*>(p.cullA); sB = const_cast<float4*>(p.cullB); sC = const_cast<float2*>(p.cullC); sR = const_cast<float*>(p.radius);
+        sv.A = p.cullA; sv.B = p.cullB; sv.G = p.sphere_geom;
         lists = reinterpret_cast<uint32_t*>(smem) + threadIdx.x;
-        return;
+        return sv;
     }
-    sA = reinterpret_cast<float4*>(smem);
-    sB = sA + np;
-    sC = reinterpret_cast<float2*>(sB + np);
-    sR = reinterpret_cast<float*>(sC + np);
-    lists = reinterpret_cast<uint32_t*>(sR + 2 * np) + threadIdx.x;
-    for (int i = threadIdx.x; i < np; i += blockDim.x) { sA[i] = p.cullA[i]; sB[i] = p.cullB[i]; sC[i] = p.cullC[i]; }
-    for (int i = threadIdx.x; i < 2 * np; i += blockDim.x) sR[i] = p.radius[i];
+    float4* sA = reinterpret_cast<float4*>(smem);
+    float4* sB = sA + np;
+    float4* sG = sB + np;
+    lists = reinterpret_cast<uint32_t*>(sG + 2 * np) + threadIdx.x;
+    for (int i = threadIdx.x; i < np; i += blockDim.x) { sA[i] = p.cullA[i]; sB[i] = p.cullB[i]; }
+    for (int i = threadIdx.x; i < 2 * np; i += blockDim.x) sG[i] = p.sphere_geom[i];
     __syncthreads();
+    sv.A = sA; sv.B = sB; sv.G = sG;
+    return sv;
+}
+// (cx, cy, cz, r) of the sphere in `slot`: brute force -> the world-space copy; hierarchy -> the image's pair arrays + radii
+template <int MODE_>
+__device__ __forceinline__ float4 sphere_at(const SceneView& sv, const float4* sA, const float4* sB, const float* sR, int slot) {
+    if constexpr (MODE_ == 2) {
+        const float* fa = reinterpret_cast<const float*>(sA) + (slot >> 1) * 4 + (slot & 1);
+        return make_float4(fa[0], fa[2], reinterpret_cast<const float*>(sB)[(slot >> 1) * 4 + (slot & 1)], sR[slot]);
+    } else return sv.G[slot];
 }
 #if RT_FLAT_EXACT
 // This warp's queue, behind the candidate lists: [best keys 32 x 8 B][tasks RT_WQ_CAP x 4 B][occlusion word, 8 B] per warp.
@@ -220,12 +232,12 @@ enum { MODE_CULL = 0, MODE_NO_CULL = 1, MODE_ACCEL = 2, MODE_CULL_GLOBAL = 3 }; 
 template <int MODE, bool HALTON = false, int GSHIFT = 5>
 __global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : RT_MAX_TPB) rt_render_kernel(const RenderParams p) {
     extern __shared__ __align__(256) unsigned char smem[];
-    float4 *sA = nullptr, *sB = nullptr; float2* sC = nullptr; float* sR = nullptr; uint32_t* lists = nullptr;
+    float4 *sA = nullptr, *sB = nullptr; float* sR = nullptr; uint32_t* lists = nullptr; SceneView sv{nullptr, nullptr, nullptr, nullptr};
     AccelSmem av{};
     if constexpr (MODE == MODE_ACCEL) {
         av = stage_accel(p.accel, smem);
         sA = const_cast<float4*>(av.sA); sB = const_cast<float4*>(av.sB); sR = const_cast<float*>(av.sR);
-    } else stage_scene(p, sA, sB, sC, sR, lists, smem);
+    } else sv = stage_scene(p, lists, smem);
     const int lstride = static_cast<int>(blockDim.x);
     WarpQueue wq{nullptr, nullptr, nullptr};
 #if RT_FLAT_EXACT
@@ -288,7 +300,7 @@ __global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : RT_MAX
         // ---- K2+K3: fused closest-hit / shadow query over every sphere ----
         QueryResult q;
         if constexpr (MODE == MODE_ACCEL) q = fused_query_accel<GSHIFT>(av, p.accel, lstride, o, d, Ldir, invL, active && want_closest, active && want_shadow, acnt);
-        else q = fused_query<MODE == MODE_NO_CULL>(sA, sB, sC, sR, lists, lstride, p.n_groups, p.n_spheres, o, d, Ldir, active && want_closest, active && want_shadow, wq);
+        else q = fused_query<MODE == MODE_NO_CULL>(sv, lists, lstride, p.n_groups, p.n_spheres, o, d, Ldir, active && want_closest, active && want_shadow, wq);
         ++n_pass;
 
         // ---- K4: integrate ----
@@ -302,9 +314,9 @@ __global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : RT_MAX
                     want_closest = false;
                 } else {
                     const int idx = q.idx, slot = (MODE == MODE_ACCEL) ? q.slot : q.idx;
-                    const float* fa = reinterpret_cast<const float*>(sA) + (slot >> 1) * 4 + (slot & 1);
-                    const V3 ctr = mk3(fa[0], fa[2], reinterpret_cast<const float*>(sB)[(slot >> 1) * 4 + (slot & 1)]);
-                    const float radius = sR[slot];
+                    const float4 sg = sphere_at<MODE>(sv, sA, sB, sR, slot);
+                    const V3 ctr = mk3(sg.x, sg.y, sg.z);
+                    const float radius = sg.w;
                     const V3 pos = mk3(q.t * d.x + o.x, q.t * d.y + o.y, q.t * d.z + o.z);   // ray-tracing.cpp:61
                     const V3 n = (pos - ctr) / radius;                                   // :62
                     const float tu = 0.5f * n.x + 0.5f, tv = 0.5f * n.z + 0.5f;          // :36-37
@@ -383,10 +395,10 @@ template <int MODE, int GSHIFT = 5>
 __global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : (MODE == MODE_NO_CULL || RT_FIRST_RAYS == 1) ? RT_MAX_TPB : RT_FIRST_MAX_TPB)
 rt_first_hit_kernel(const RenderParams p) {
     extern __shared__ __align__(256) unsigned char smem[];
-    float4 *sA = nullptr, *sB = nullptr; float2* sC = nullptr; float* sR = nullptr; uint32_t* lists = nullptr;
+    float4 *sA = nullptr, *sB = nullptr; float* sR = nullptr; uint32_t* lists = nullptr; SceneView sv{nullptr, nullptr, nullptr, nullptr};
     AccelSmem av{};
     if constexpr (MODE == MODE_ACCEL) av = stage_accel(p.accel, smem);
-    else stage_scene<MODE == MODE_CULL_GLOBAL>(p, sA, sB, sC, sR, lists, smem);
+    else sv = stage_scene<MODE == MODE_CULL_GLOBAL>(p, lists, smem);
     AccelCounters acnt; acnt.group_visits = 0u;
     const unsigned FULL = 0xffffffffu;
     const unsigned lane = threadIdx.x & 31u;
@@ -427,8 +439,8 @@ rt_first_hit_kernel(const RenderParams p) {
             }
             if constexpr (R == 1) {
                 if constexpr (MODE == MODE_ACCEL) q[0] = fused_query_accel<GSHIFT, RAYS_CLOSEST>(av, p.accel, static_cast<int>(blockDim.x), o[0], d[0], Ldir, mk3(p.iLx, p.iLy, p.iLz), want[0], false, acnt);
-                else q[0] = fused_query<MODE == MODE_NO_CULL, RAYS_CLOSEST>(sA, sB, sC, sR, lists, static_cast<int>(blockDim.x), p.n_groups, p.n_spheres, o[0], d[0], Ldir, want[0], false);
-            } else closest_query_multi<R>(sA, sB, sR, lists, static_cast<int>(blockDim.x), p.n_groups, p.n_spheres, o, d, want, q);
+                else q[0] = fused_query<MODE == MODE_NO_CULL, RAYS_CLOSEST>(sv, lists, static_cast<int>(blockDim.x), p.n_groups, p.n_spheres, o[0], d[0], Ldir, want[0], false);
+            } else closest_query_multi<R>(sv, lists, static_cast<int>(blockDim.x), p.n_groups, p.n_spheres, o, d, want, q);
 #pragma unroll
             for (int j = 0; j < R; ++j) {
                 const int kk = k + j;
@@ -460,12 +472,12 @@ enum PathLaneState { PS_NEED_ITEM = 0, PS_SCAN = 1, PS_HIT_NEW = 2, PS_SHADE = 3
 template <int MODE, bool HALTON = false, int GSHIFT = 5, bool DIRECT_ONLY = false>
 __global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : RT_MAX_TPB) rt_path_kernel(const RenderParams p) {
     extern __shared__ __align__(256) unsigned char smem[];
-    float4 *sA = nullptr, *sB = nullptr; float2* sC = nullptr; float* sR = nullptr; uint32_t* lists = nullptr;
+    float4 *sA = nullptr, *sB = nullptr; float* sR = nullptr; uint32_t* lists = nullptr; SceneView sv{nullptr, nullptr, nullptr, nullptr};
     AccelSmem av{};
     if constexpr (MODE == MODE_ACCEL) {
         av = stage_accel(p.accel, smem);
         sA = const_cast<float4*>(av.sA); sB = const_cast<float4*>(av.sB); sR = const_cast<float*>(av.sR);
-    } else stage_scene<MODE == MODE_CULL_GLOBAL>(p, sA, sB, sC, sR, lists, smem);
+    } else sv = stage_scene<MODE == MODE_CULL_GLOBAL>(p, lists, smem);
     const int lstride = static_cast<int>(blockDim.x);
     const V3 invL = mk3(p.iLx, p.iLy, p.iLz);
     AccelCounters acnt; acnt.group_visits = 0u;
@@ -543,10 +555,10 @@ __global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : RT_MAX
             const float u = div_rn(static_cast<float>(px) + jx, static_cast<float>(p.W));
             const float v = div_rn(static_cast<float>(py) + jy, static_cast<float>(p.H));
             camera_get_ray(p.cam, u, v, lx, ly, o, d);
-            const float* fa = reinterpret_cast<const float*>(sA) + (hit_slot >> 1) * 4 + (hit_slot & 1);
+            const float4 sg = sphere_at<MODE>(sv, sA, sB, sR, hit_slot);
             const float a = dot3(d, d);
             hit_t = 0.f;
-            sphere_exact(fa[0], fa[2], reinterpret_cast<const float*>(sB)[(hit_slot >> 1) * 4 + (hit_slot & 1)], sR[hit_slot], o, d, a, rcp_refined(a), false, hit_t);
+            sphere_exact(sg.x, sg.y, sg.z, sg.w, o, d, a, rcp_refined(a), false, hit_t);
             T = mk3(1.f, 1.f, 1.f); Lsum = mk3(0.f, 0.f, 0.f);
             depth = 0; want_shadow = false;
             st = PS_SHADE;
@@ -557,9 +569,9 @@ __global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : RT_MAX
             const int slot = hit_slot;
             int idx = slot;
             if constexpr (MODE == MODE_ACCEL) idx = av.sI[slot];
-            const float* fa = reinterpret_cast<const float*>(sA) + (slot >> 1) * 4 + (slot & 1);
-            const V3 ctr = mk3(fa[0], fa[2], reinterpret_cast<const float*>(sB)[(slot >> 1) * 4 + (slot & 1)]);
-            const float radius = sR[slot];
+            const float4 sg = sphere_at<MODE>(sv, sA, sB, sR, slot);
+            const V3 ctr = mk3(sg.x, sg.y, sg.z);
+            const float radius = sg.w;
             const V3 pos = mk3(hit_t * d.x + o.x, hit_t * d.y + o.y, hit_t * d.z + o.z);   // ray-tracing.cpp:61
             const V3 n = (pos - ctr) / radius;                                   // :62
             const float tu = 0.5f * n.x + 0.5f, tv = 0.5f * n.z + 0.5f;          // :36-37
@@ -591,7 +603,7 @@ __global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : RT_MAX
         const bool active = (st == PS_QUERY);
         QueryResult q;
         if constexpr (MODE == MODE_ACCEL) q = fused_query_accel<GSHIFT, kRays>(av, p.accel, lstride, o, d, Ldir, invL, active && want_closest, active && want_shadow, acnt);
-        else q = fused_query<MODE == MODE_NO_CULL, kRays>(sA, sB, sC, sR, lists, lstride, p.n_groups, p.n_spheres, o, d, Ldir, active && want_closest, active && want_shadow);
+        else q = fused_query<MODE == MODE_NO_CULL, kRays>(sv, lists, lstride, p.n_groups, p.n_spheres, o, d, Ldir, active && want_closest, active && want_shadow);
         ++n_pass;
 
         // ---- resolve the pass ----
@@ -703,10 +715,10 @@ __global__ void __launch_bounds__(256) rt_resolve_kernel(const float4* __restric
 template <int MODE, int GSHIFT = 5>
 __global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : RT_MAX_TPB) rt_primary_kernel(const RenderParams p, int32_t* __restrict__ sphere_idx, int32_t* __restrict__ material_id) {
     extern __shared__ __align__(256) unsigned char smem[];
-    float4 *sA = nullptr, *sB = nullptr; float2* sC = nullptr; float* sR = nullptr; uint32_t* lists = nullptr;
+    float4 *sA = nullptr, *sB = nullptr; float* sR = nullptr; uint32_t* lists = nullptr; SceneView sv{nullptr, nullptr, nullptr, nullptr};
     AccelSmem av{};
     if constexpr (MODE == MODE_ACCEL) av = stage_accel(p.accel, smem);
-    else stage_scene<MODE == MODE_CULL_GLOBAL>(p, sA, sB, sC, sR, lists, smem);
+    else sv = stage_scene<MODE == MODE_CULL_GLOBAL>(p, lists, smem);
     AccelCounters acnt; acnt.group_visits = 0u;
     const u64 n_items = static_cast<u64>(p.tiles_x) * p.tiles_y * 32ull;
     for (u64 item = blockIdx.x * static_cast<u64>(blockDim.x) + threadIdx.x; item < ((n_items + 31ull) & ~31ull); item += static_cast<u64>(gridDim.x) * blockDim.x) {
@@ -723,7 +735,7 @@ __global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : RT_MAX
         }
         QueryResult q;
         if constexpr (MODE == MODE_ACCEL) q = fused_query_accel<GSHIFT>(av, p.accel, static_cast<int>(blockDim.x), o, d, mk3(p.Lx, p.Ly, p.Lz), mk3(p.iLx, p.iLy, p.iLz), valid, false, acnt);
-        else q = fused_query<MODE == MODE_NO_CULL>(sA, sB, sC, sR, lists, static_cast<int>(blockDim.x), p.n_groups, p.n_spheres, o, d, mk3(p.Lx, p.Ly, p.Lz), valid, false);
+        else q = fused_query<MODE == MODE_NO_CULL>(sv, lists, static_cast<int>(blockDim.x), p.n_groups, p.n_spheres, o, d, mk3(p.Lx, p.Ly, p.Lz), valid, false);
         if (valid) {
             const int pix = py * p.W + px;
             if (sphere_idx) sphere_idx[pix] = q.idx;

@@ -26,8 +26,8 @@ enum { WF_WANT_CLOSEST = 1, WF_WANT_SHADOW = 2, WF_LIVE = 4, WF_DONE = 8, WF_OCC
 template <bool NO_CULL>
 __global__ void RT_RENDER_BOUNDS wf_intersect_kernel(const RenderParams p, const WfState s) {
     extern __shared__ __align__(256) unsigned char smem[];
-    float4 *sA, *sB; float2* sC; float* sR; uint32_t* lists;
-    stage_scene(p, sA, sB, sC, sR, lists, smem);
+    uint32_t* lists;
+    const SceneView sv = stage_scene(p, lists, smem);
     const V3 Ldir = mk3(p.Lx, p.Ly, p.Lz);
     for (int slot = blockIdx.x * blockDim.x + threadIdx.x; slot < s.n_slots; slot += gridDim.x * blockDim.x) {
         const int4 id = s.ids[slot];
@@ -35,7 +35,7 @@ __global__ void RT_RENDER_BOUNDS wf_intersect_kernel(const RenderParams p, const
         if (__all_sync(0xffffffffu, !live)) continue;
         float4 o4 = s.o[slot], d4 = s.d[slot];
         const V3 o = mk3(o4.x, o4.y, o4.z), d = live ? mk3(d4.x, d4.y, d4.z) : mk3(0.f, 0.f, 1.f);
-        const QueryResult q = fused_query<NO_CULL>(sA, sB, sC, sR, lists, static_cast<int>(blockDim.x), p.n_groups, p.n_spheres, o, d, Ldir,
+        const QueryResult q = fused_query<NO_CULL>(sv, lists, static_cast<int>(blockDim.x), p.n_groups, p.n_spheres, o, d, Ldir,
                                                    live && (id.w & WF_WANT_CLOSEST), live && (id.w & WF_WANT_SHADOW));
         if (live) {
             o4.w = q.t; d4.w = __int_as_float(q.idx);

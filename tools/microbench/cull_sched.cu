@@ -79,6 +79,47 @@ template <int R> __global__ void __launch_bounds__(896) k_r(const CullRay* rays,
     }
     out[blockIdx.x * blockDim.x + threadIdx.x] = acc;
 }
+// What do the sign-collecting funnel shifts cost?  Fused loop (closest + shadow) with the per-value SHF replaced by
+//   COLLECT 0: SHF.L.W (as in the kernels)   1: one LOP3 xor per value (same count, no shift)   2: F2FP pack of the two halves to f16x2
+//   (signs land in bits 15 / 31 of ONE word) + one xor per PAIR   3: nothing per value: a packed FADD2 accumulates the discriminants
+template <int COLLECT> __global__ void __launch_bounds__(896) k_c(const CullRay* rays, const float4* g, int np, int iters, uint32_t* out) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    float4* sA = reinterpret_cast<float4*>(smem); float4* sB = sA + np;
+    for (int i = threadIdx.x; i < np * 5 / 2; i += blockDim.x) sA[i] = g[i];
+    __syncthreads();
+    CullRay r = rays[blockIdx.x * blockDim.x + threadIdx.x];
+    uint32_t acc = 0;
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll 1
+        for (int gi = 0; gi < np / 16; ++gi) {
+            uint32_t mc = 0, ms = 0; u64 sc = 0, ss = 0;
+#pragma unroll
+            for (int q = 0; q < 16; ++q) {
+                const float4 A = sA[gi * 16 + q], B = sB[gi * 16 + q];
+                const u64 cx = pk2(A.x, A.y), cy = pk2(A.z, A.w), cz = pk2(B.x, B.y);
+                u64 nc2 = fadd2(pk2(B.z, B.w), bc2(r.noo));
+                nc2 = ffma2(bc2(r.oz2), cz, nc2); nc2 = ffma2(bc2(r.oy2), cy, nc2); nc2 = ffma2(bc2(r.ox2), cx, nc2);
+                u64 b1 = ffma2(bc2(r.ndz), cz, bc2(r.od)); b1 = ffma2(bc2(r.ndy), cy, b1); b1 = ffma2(bc2(r.ndx), cx, b1);
+                const u64 d1 = ffma2(b1, b1, nc2);
+                const u64 b2 = ffma2(bc2(-1.0f), cz, bc2(r.oL));
+                const u64 d2 = ffma2(b2, b2, nc2);
+                uint32_t l1, h1, l2, h2; upk2(d1, l1, h1); upk2(d2, l2, h2);
+                if (COLLECT == 0) { mc = __funnelshift_l(l1, mc, 1); mc = __funnelshift_l(h1, mc, 1); ms = __funnelshift_l(l2, ms, 1); ms = __funnelshift_l(h2, ms, 1); }
+                else if (COLLECT == 1) { mc ^= l1; mc ^= h1 >> 1; ms ^= l2; ms ^= h2 >> 1; }
+                else if (COLLECT == 2) {
+                    uint32_t p1, p2;
+                    asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(p1) : "f"(__uint_as_float(h1)), "f"(__uint_as_float(l1)));
+                    asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(p2) : "f"(__uint_as_float(h2)), "f"(__uint_as_float(l2)));
+                    mc = __funnelshift_l(p1 & 0x80008000u, mc, 1) ^ p1; ms = __funnelshift_l(p2 & 0x80008000u, ms, 1) ^ p2;
+                } else { sc = fadd2(sc, d1); ss = fadd2(ss, d2); }
+            }
+            if (COLLECT == 3) { uint32_t a0, a1, a2, a3; upk2(sc, a0, a1); upk2(ss, a2, a3); mc = a0 ^ a1; ms = a2 ^ a3; }
+            acc += __popc(~mc) + 3 * __popc(~ms);
+        }
+        r.noo += 1e-7f * static_cast<float>(acc & 1u);
+    }
+    out[blockIdx.x * blockDim.x + threadIdx.x] = acc;
+}
 template <class F> float timeit(F f) { cudaEvent_t a, b; cudaEventCreate(&a); cudaEventCreate(&b); f(); cudaDeviceSynchronize(); cudaEventRecord(a); f(); cudaEventRecord(b); cudaEventSynchronize(b); float ms; cudaEventElapsedTime(&ms, a, b); return ms; }
 int main() {
     cudaDeviceProp p; cudaGetDeviceProperties(&p, 0);
@@ -100,5 +141,10 @@ int main() {
         const double pairs = (double)grid * tpb / 32.0 * iters * np * R;   /* warp-level pair evaluations per ray */ \
         printf("C  %d rays per lane: %8.3f ms  %6.2f clk per pair and ray per SMSP %s\n", R, ms, ms * 1e-3 * p.clockRate * 1e3 / (pairs / (sms * 4)), e ? cudaGetErrorString(e) : ""); }
     RUNR(1) RUNR(2) RUNR(3) RUNR(4)
+#define RUNC(Cc) { cudaFuncSetAttribute(k_c<Cc>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+        const float ms = timeit([&] { k_c<Cc><<<grid, tpb, smem>>>(rays, g, np, iters, out); }); const cudaError_t e = cudaGetLastError(); \
+        const double pairs = (double)grid * tpb / 32.0 * iters * np; \
+        printf("CS light-aligned (2 LDS), sign collection %d: %8.3f ms  %6.2f clk per pair per SMSP %s\n", Cc, ms, ms * 1e-3 * p.clockRate * 1e3 / (pairs / (sms * 4)), e ? cudaGetErrorString(e) : ""); }
+    RUNC(0) RUNC(1) RUNC(2) RUNC(3)
     return 0;
 }
