@@ -88,15 +88,54 @@ def test_render_matches_oracle_path_for_path(gpu, orc, scene_factory, name, w, h
     assert (st.paths, st.closest_rays, st.shadow_rays) == (ost.paths, ost.closest_rays, ost.shadow_rays)
 
 
-def test_cull_is_result_neutral(gpu, scene_factory):
+@pytest.mark.parametrize("case", ["d488", "s4096", "far_camera", "light_near_an_axis", "three_lights", "random_big_radii"])
+def test_cull_is_result_neutral(gpu, scene_factory, case):
+    """The conservative cull (packed FMAs in the light-aligned frame, rt_device.cuh) must never drop a sphere the exact test accepts:
+    the same kernels with every sphere sent through the exact test (RT_FLAG_DEBUG_NO_CULL) give the same bytes and ray counters --
+    on the named scenes, from a camera 150 units away (large |o|: the slack is relative), with a light direction a hair off an
+    axis and with several lights (each has its own frame), and on random scenes with a wide radius spread."""
     rt = gpu
-    scene, _ = scene_factory("d488")
-    r = _renderer(rt, scene, rt.scenes.default_camera(), 256, 144)
-    r.render(3, 50, 0)
-    a = r.read_hdr_sum()
-    r.clear()
-    r.render(3, 50, rt.RT_FLAG_DEBUG_NO_CULL)
-    assert np.array_equal(a, r.read_hdr_sum())
+    w, h, spp, depth = 256, 144, 3, 50
+    cam = rt.scenes.default_camera()
+    if case in ("d488", "s4096"):
+        scene, _ = scene_factory(case)
+        if case == "s4096":
+            w, h, spp, depth = 128, 72, 2, 8
+    elif case == "far_camera":
+        scene, _ = scene_factory("d488")
+        cam = rt.Camera((140.0, 45.0, -38.0), (0.0, 1.0, 0.0), 3.0, w / h, 150.0, 0.4)
+    elif case == "light_near_an_axis":
+        scene = rt.scenes.build_scene(-6, 6, seed=9)
+        scene = rt.Scene.from_flat(_with_lights(scene.export(), [((1e-4, 1.0, -2e-5), 40000.0)]))
+    elif case == "three_lights":
+        scene = rt.scenes.scene_d488()
+        scene.add_light(rt.DirectionalLight((-1.0, 0.6, 0.2), rt.XMCOLOR(0.3, 0.5, 1.0), 25000.0))
+        scene.add_light(rt.DirectionalLight((0.0, 0.0, -1.0), rt.XMCOLOR(1.0, 0.4, 0.3), 15000.0))
+    else:
+        scene = _random_scene(rt, np.random.default_rng(41), 700, 60.0, 14.0, True)
+        cam = rt.Camera((11.0, 2.5, 9.0), (0.0, 0.5, 0.0), 40.0, w / h, 13.0, 0.1)
+    r = _renderer(rt, scene, cam, w, h)
+    r.reset_stats(); r.render(spp, depth, 0)
+    a, sa = r.read_hdr_sum(), r.stats()
+    ia = r.primary_hits(1, 0)
+    r.clear(); r.reset_stats()
+    r.render(spp, depth, rt.RT_FLAG_DEBUG_NO_CULL)
+    b, sb = r.read_hdr_sum(), r.stats()
+    ib = r.primary_hits(1, rt.RT_FLAG_DEBUG_NO_CULL)
+    assert np.array_equal(a, b, equal_nan=True)
+    assert (sa.paths, sa.closest_rays, sa.shadow_rays) == (sb.paths, sb.closest_rays, sb.shadow_rays)
+    assert np.array_equal(ia[0], ib[0]) and np.array_equal(ia[1], ib[1])
+
+
+def _with_lights(flat, lights):
+    """The flat scene with its lights replaced by [((dx, dy, dz), luminance), ...] (white)."""
+    import copy
+    f = copy.deepcopy(flat)
+    L = np.zeros(len(lights), f.lights.dtype)
+    for i, (d, lum) in enumerate(lights):
+        L["dir"][i] = d; L["color"][i] = (1.0, 1.0, 1.0, 1.0); L["luminance"][i] = lum
+    f.lights = L
+    return f
 
 
 def test_deterministic_and_resumable(gpu, scene_factory):
