@@ -63,10 +63,10 @@ def main():
             + ranges("rt_device.cuh", [("vector_math", r"^struct V3"), ("materials_math", r"XMVector3RefractV"), ("rng_halton", r"Counter-based RNG"),
                                        ("camera_texture", r"^struct DevCamera"), ("sphere_exact", r"bool sphere_exact"), ("ffma2_fadd2", r"u64 pk2\("),
                                        ("brute_cull_lists", r"^struct QueryResult"), ("exact_candidate", r"bool exact_candidate"),
-                                       ("brute_cull_pair", r"^struct CullRay "), ("brute_query", r"QueryResult fused_query\(")])
-            + ranges("rt_kernels.cuh", [("stage_scene", r"void stage_scene"), ("direct_light", r"V3 direct_unshadowed"), ("scatter", r"bool scatter\("),
+                                       ("brute_cull_pair", r"^struct CullRay "), ("brute_query", r"QueryResult fused_query\("), ("first_hit_multi_query", r"void closest_query_multi")])
+            + ranges("rt_kernels.cuh", [("stage_scene", r"SceneView stage_scene"), ("direct_light", r"V3 direct_unshadowed"), ("scatter", r"bool scatter\("),
                                         ("halton_draw", r"void draw_halton"), ("work_items", r"bool item_to_pixel"), ("one_kernel_path_loop", r"void .*rt_render_kernel"),
-                                        ("first_hit_kernel", r"void .*rt_first_hit_kernel"), ("path_setup", r"void .*rt_path_kernel"),
+                                        ("first_hit_kernel", r"^rt_first_hit_kernel\(const RenderParams p\)"), ("path_setup", r"void .*rt_path_kernel"),
                                         ("path_regeneration", r"// ---- regeneration: work items"), ("path_primary_vertex", r"// ---- K1 again for the regenerated"),
                                         ("path_shade_glue", r"// ---- K4 at the vertex in hand"), ("path_query_call", r"fused closest-hit / shadow query ----\s*$"),
                                         ("path_resolve", r"// ---- resolve the pass"), ("path_stats", r"primary rays were counted by stage 1"),
