@@ -384,6 +384,18 @@ __global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : RT_MAX
 // Arithmetic per path is unchanged (same device functions, same order), so the bits are those of the one-kernel schedule.
 // ------------------------------------------------------------------------------------------------------------------
 
+// First-hit records are written once and read once: RT_REC_STREAM = 1 marks both sides as streaming (evict-first), so that the
+// records do not push the running-sum / partial-sum lines out of L2 before their half-sector stores have merged.
+#ifndef RT_REC_STREAM
+#define RT_REC_STREAM 0
+#endif
+#if RT_REC_STREAM
+#define RT_REC_LOAD(ptr) __ldcs(ptr)
+#define RT_REC_STORE(ptr, v) __stcs(ptr, v)
+#else
+#define RT_REC_LOAD(ptr) __ldg(ptr)
+#define RT_REC_STORE(ptr, v) (*(ptr) = (v))
+#endif
 #ifndef RT_FIRST_RAYS
 #define RT_FIRST_RAYS 4    /* frames per lane and query of the brute-force first-hit stage (1, 2 or 4) */
 #endif
@@ -451,8 +463,8 @@ rt_first_hit_kernel(const RenderParams p) {
         if (valid) {                                         // two 16-byte stores into one aligned 32-byte sector: no partial-sector write reaches HBM
             const size_t pix = static_cast<size_t>(py) * p.W + px;
             uint4* dst = reinterpret_cast<uint4*>(p.hits + pix * p.hit_stride + static_cast<size_t>(g) * 16);
-            dst[0] = make_uint4(static_cast<uint32_t>(rec0), static_cast<uint32_t>(rec0 >> 32), static_cast<uint32_t>(rec1), static_cast<uint32_t>(rec1 >> 32));
-            dst[1] = make_uint4(static_cast<uint32_t>(rec2), static_cast<uint32_t>(rec2 >> 32), static_cast<uint32_t>(rec3), static_cast<uint32_t>(rec3 >> 32));
+            RT_REC_STORE(dst, make_uint4(static_cast<uint32_t>(rec0), static_cast<uint32_t>(rec0 >> 32), static_cast<uint32_t>(rec1), static_cast<uint32_t>(rec1 >> 32)));
+            RT_REC_STORE(dst + 1, make_uint4(static_cast<uint32_t>(rec2), static_cast<uint32_t>(rec2 >> 32), static_cast<uint32_t>(rec3), static_cast<uint32_t>(rec3 >> 32)));
         }
     }
     u64 c0 = n_closest;
@@ -531,7 +543,7 @@ __global__ void __launch_bounds__(MODE == MODE_ACCEL ? RT_ACCEL_MAX_TPB : RT_MAX
                         st = PS_NEED_ITEM;
                         break;
                     }
-                    if ((s_cur & 7) == 0) rec = __ldg(reinterpret_cast<const uint4*>(p.hits + static_cast<size_t>(pix) * p.hit_stride + s_cur));
+                    if ((s_cur & 7) == 0) rec = RT_REC_LOAD(reinterpret_cast<const uint4*>(p.hits + static_cast<size_t>(pix) * p.hit_stride + s_cur));
                     const int f = s_cur & 7;
                     const uint32_t w = (f < 2) ? rec.x : (f < 4) ? rec.y : (f < 6) ? rec.z : rec.w;
                     const uint32_t v16 = (w >> (16 * (f & 1))) & 0xffffu;
