@@ -49,6 +49,11 @@ class AccelImageInfo(C.Structure):
                 ("c_max", C.c_float)]
 
 
+class CullImageInfo(C.Structure):
+    _fields_ = [("bytes", C.c_size_t), ("n_spheres", C.c_int32), ("n_pairs", C.c_int32), ("off_B", C.c_int32), ("off_G", C.c_int32),
+                ("rot", C.c_float * 9), ("light_dir", C.c_float * 3)]
+
+
 class Stats(C.Structure):
     _fields_ = [("paths", C.c_uint64), ("closest_rays", C.c_uint64), ("shadow_rays", C.c_uint64),
                 ("sphere_tests", C.c_uint64), ("passes", C.c_uint64), ("render_ms", C.c_double),
@@ -107,6 +112,7 @@ SYMBOLS = [
     ("rt_hdr_bind_external", C.c_int, [_P, _P]),
     ("rt_scene_accel_image", C.c_int, [_P, _P, C.c_size_t, C.POINTER(AccelImageInfo)]),
     ("rt_scene_accel_image_slots", C.c_int, [_P, C.c_int, _P, C.c_size_t, C.POINTER(AccelImageInfo)]),
+    ("rt_scene_cull_image", C.c_int, [_P, C.c_int, _P, C.c_size_t, C.POINTER(CullImageInfo)]),
     ("rt_get_stats", C.c_int, [_P, C.POINTER(Stats)]),
     ("rt_stats_reset", C.c_int, [_P]),
     ("rt_build_info", C.c_char_p, []),

@@ -149,6 +149,16 @@ class Scene:
         L.check(self._lib.rt_scene_accel_image_slots(self._h, min_group_slots, buf.ctypes.data_as(C.c_void_p), buf.nbytes, C.byref(info)))
         return info, buf
 
+    def cull_image(self, light_index: int = 0):
+        """(info, A (np, 4), B (np, 4), G (2 np, 4)) float32: the arrays the brute-force query stages for light `light_index`
+        (-1: no light) -- pair arrays in the light-aligned frame + world-space (c, r); rt_scene_cull_image, host only."""
+        info = L.CullImageInfo()
+        L.check(self._lib.rt_scene_cull_image(self._h, light_index, None, 0, C.byref(info)))
+        buf = np.zeros(info.bytes, dtype=np.uint8)
+        L.check(self._lib.rt_scene_cull_image(self._h, light_index, buf.ctypes.data_as(C.c_void_p), buf.nbytes, C.byref(info)))
+        f = buf.view(np.float32)
+        return (info, f[: info.off_B // 4].reshape(-1, 4), f[info.off_B // 4: info.off_G // 4].reshape(-1, 4), f[info.off_G // 4:].reshape(-1, 4))
+
     # -- low-level recorder (ids) --
     def add_texture(self, tex: Texture) -> int:
         key = id(tex)

@@ -531,6 +531,47 @@ static int build_accel(rt_context* c, const rt_scene* s) {
     return RT_OK;
 }
 
+// ------------------------------------------------------------------------------------------------
+// Pair arrays of the brute-force cull in the light-aligned frame (rt_device.cuh, SceneView): rows of `rot` = (e1, e2, L), c' = rot c,
+// everything in double, one rounding to float per coordinate.  w = r^2 - |c|^2 + k (|c|^2 + r^2) is rotation invariant.  Host only
+// (no CUDA call): rt_set_scene uploads the result, rt_scene_cull_image hands it to the CPU tests.
+// ------------------------------------------------------------------------------------------------
+static void light_frame(const host::V3& Lu, bool lit, double rot[9]) {
+    if (!lit) { const double id[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1}; std::copy(id, id + 9, rot); return; }
+    double L[3] = {Lu.x, Lu.y, Lu.z};
+    const double ln = std::sqrt(L[0] * L[0] + L[1] * L[1] + L[2] * L[2]);
+    for (double& v : L) v /= ln;
+    const int ax = std::fabs(L[0]) <= std::fabs(L[1]) ? (std::fabs(L[0]) <= std::fabs(L[2]) ? 0 : 2) : (std::fabs(L[1]) <= std::fabs(L[2]) ? 1 : 2);
+    double u[3] = {0, 0, 0}; u[ax] = 1.0;                               // the axis least aligned with L
+    double e1[3] = {u[1] * L[2] - u[2] * L[1], u[2] * L[0] - u[0] * L[2], u[0] * L[1] - u[1] * L[0]};
+    const double n1 = std::sqrt(e1[0] * e1[0] + e1[1] * e1[1] + e1[2] * e1[2]);
+    for (double& v : e1) v /= n1;
+    const double e2[3] = {L[1] * e1[2] - L[2] * e1[1], L[2] * e1[0] - L[0] * e1[2], L[0] * e1[1] - L[1] * e1[0]};
+    for (int k = 0; k < 3; ++k) { rot[k] = e1[k]; rot[3 + k] = e2[k]; rot[6 + k] = L[k]; }
+}
+static void fill_pairs(const rt_scene* s, int np, const double rot[9], float4* Ao, float4* Bo) {
+    const int n = static_cast<int>(s->spheres.size());
+    const double K = static_cast<double>(RT_CULL_K);
+    for (int p = 0; p < np; ++p) {
+        float v[2][4];
+        for (int h = 0; h < 2; ++h) {
+            const int i = 2 * p + h;
+            if (i >= n) { v[h][0] = v[h][1] = v[h][2] = 0.f; v[h][3] = RT_PAD_W; continue; }
+            const rt_sphere_desc& sp = s->spheres[i];
+            const double cw[3] = {sp.cx, sp.cy, sp.cz};
+            for (int k = 0; k < 3; ++k) v[h][k] = static_cast<float>(rot[3 * k] * cw[0] + rot[3 * k + 1] * cw[1] + rot[3 * k + 2] * cw[2]);
+            const double cc = cw[0] * cw[0] + cw[1] * cw[1] + cw[2] * cw[2], r2 = static_cast<double>(sp.radius) * sp.radius;
+            v[h][3] = static_cast<float>(r2 - cc + K * (cc + r2));      // -(|c|^2 - r^2) + slack
+        }
+        Ao[p] = make_float4(v[0][0], v[1][0], v[0][1], v[1][1]);
+        Bo[p] = make_float4(v[0][2], v[1][2], v[0][3], v[1][3]);
+    }
+}
+static void fill_geom(const rt_scene* s, int n_pad, float4* G) {
+    for (int i = 0; i < n_pad; ++i) G[i] = make_float4(0.f, 0.f, 0.f, 1.f);
+    for (size_t i = 0; i < s->spheres.size(); ++i) G[i] = make_float4(s->spheres[i].cx, s->spheres[i].cy, s->spheres[i].cz, s->spheres[i].radius);
+}
+
 extern "C" {
 
 int rt_context_create(int device, rt_context** out) {
@@ -621,41 +662,9 @@ int rt_set_scene(rt_context* c, const rt_scene* s) {
     const double L[3] = {Ln.x, Ln.y, Ln.z};
     std::vector<float4> A(np), B(np);
     std::vector<rt::DevMat> M(std::max(n, 1));
-    // Pair arrays of the cull in the light-aligned frame of light 0 (rt_device.cuh, SceneView): rows of `rot` = (e1, e2, L), c' = rot c,
-    // everything in double, one rounding to float per coordinate.  w = r^2 - |c|^2 + k (|c|^2 + r^2) is rotation invariant.
-    auto light_frame = [](const host::V3& Lu, bool lit, double rot[9]) {
-        if (!lit) { const double id[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1}; std::copy(id, id + 9, rot); return; }
-        double L[3] = {Lu.x, Lu.y, Lu.z};
-        const double ln = std::sqrt(L[0] * L[0] + L[1] * L[1] + L[2] * L[2]);
-        for (double& v : L) v /= ln;
-        const int ax = std::fabs(L[0]) <= std::fabs(L[1]) ? (std::fabs(L[0]) <= std::fabs(L[2]) ? 0 : 2) : (std::fabs(L[1]) <= std::fabs(L[2]) ? 1 : 2);
-        double u[3] = {0, 0, 0}; u[ax] = 1.0;                               // the axis least aligned with L
-        double e1[3] = {u[1] * L[2] - u[2] * L[1], u[2] * L[0] - u[0] * L[2], u[0] * L[1] - u[1] * L[0]};
-        const double n1 = std::sqrt(e1[0] * e1[0] + e1[1] * e1[1] + e1[2] * e1[2]);
-        for (double& v : e1) v /= n1;
-        const double e2[3] = {L[1] * e1[2] - L[2] * e1[1], L[2] * e1[0] - L[0] * e1[2], L[0] * e1[1] - L[1] * e1[0]};
-        for (int k = 0; k < 3; ++k) { rot[k] = e1[k]; rot[3 + k] = e2[k]; rot[6 + k] = L[k]; }
-    };
-    auto fill_pairs = [&](const double rot[9], float4* Ao, float4* Bo) {
-        const double K = static_cast<double>(RT_CULL_K);
-        for (int p = 0; p < np; ++p) {
-            float v[2][4];
-            for (int h = 0; h < 2; ++h) {
-                const int i = 2 * p + h;
-                if (i >= n) { v[h][0] = v[h][1] = v[h][2] = 0.f; v[h][3] = RT_PAD_W; continue; }
-                const rt_sphere_desc& sp = s->spheres[i];
-                const double cw[3] = {sp.cx, sp.cy, sp.cz};
-                for (int k = 0; k < 3; ++k) v[h][k] = static_cast<float>(rot[3 * k] * cw[0] + rot[3 * k + 1] * cw[1] + rot[3 * k + 2] * cw[2]);
-                const double cc = cw[0] * cw[0] + cw[1] * cw[1] + cw[2] * cw[2], r2 = static_cast<double>(sp.radius) * sp.radius;
-                v[h][3] = static_cast<float>(r2 - cc + K * (cc + r2));      // -(|c|^2 - r^2) + slack
-            }
-            Ao[p] = make_float4(v[0][0], v[1][0], v[0][1], v[1][1]);
-            Bo[p] = make_float4(v[0][2], v[1][2], v[0][3], v[1][3]);
-        }
-    };
     double rot0[9];
     light_frame(Ln, has_light, rot0);
-    fill_pairs(rot0, A.data(), B.data());
+    fill_pairs(s, np, rot0, A.data(), B.data());
     for (int i = 0; i < n; ++i) {
         const rt_material_desc& m = s->materials[s->spheres[i].material];
         rt::DevMat dm{}; dm.kind = m.kind; dm.smoothness = m.smoothness; dm.ior = m.ior; dm.mat_index = s->spheres[i].material;
@@ -672,8 +681,8 @@ int rt_set_scene(rt_context* c, const rt_scene* s) {
     c->n_sampler = 2 * std::max<size_t>(1, s->materials.size());
     if (int r = dev_realloc(c->sampler, 2 * c->n_sampler)) return r;    // [indices][snapshot taken before light 0's pass of a batch]
     RT_CUDA(cudaMemsetAsync(c->sampler, 0, 2 * c->n_sampler * sizeof(u64), c->stream));      // the reference's indices start at 0 with the scene
-    std::vector<float4> G(n_pad, make_float4(0.f, 0.f, 0.f, 1.f));            // padded: the kernels stage 2 * n_pairs_pad entries
-    for (int i = 0; i < n; ++i) G[i] = make_float4(s->spheres[i].cx, s->spheres[i].cy, s->spheres[i].cz, s->spheres[i].radius);
+    std::vector<float4> G(n_pad);                                              // padded: the kernels stage 2 * n_pairs_pad entries
+    fill_geom(s, n_pad, G.data());
     if (int r = dev_realloc(c->geom, G.size())) return r;
     RT_CUDA(cudaMemcpyAsync(c->geom, G.data(), G.size() * sizeof(float4), cudaMemcpyHostToDevice, c->stream));
     RT_CUDA(cudaMemcpyAsync(c->cullA, A.data(), np * sizeof(float4), cudaMemcpyHostToDevice, c->stream));
@@ -709,7 +718,7 @@ int rt_set_scene(rt_context* c, const rt_scene* s) {
             light_frame(Lk, true, rk);
             for (int q = 0; q < 9; ++q) e.rot[q] = static_cast<float>(rk[q]);
             e.cullA = c->extra_pairs + 2 * (k - 1) * np; e.cullB = e.cullA + np;
-            fill_pairs(rk, PE.data() + 2 * (k - 1) * np, PE.data() + 2 * (k - 1) * np + np);
+            fill_pairs(s, np, rk, PE.data() + 2 * (k - 1) * np, PE.data() + 2 * (k - 1) * np + np);
             c->extra_lights.push_back(e);
         }
         RT_CUDA(cudaMemcpyAsync(c->extra_pairs, PE.data(), PE.size() * sizeof(float4), cudaMemcpyHostToDevice, c->stream));
@@ -1223,6 +1232,28 @@ int rt_scene_accel_image_slots(const rt_scene* s, int min_group_slots, void* buf
     if (buf) {
         if (capacity < img.size()) return fail(RT_ERR_INVALID_ARGUMENT, "rt_scene_accel_image: buffer of %zu bytes, image needs %zu", capacity, img.size());
         std::memcpy(buf, img.data(), img.size());
+    }
+    return RT_OK;
+}
+int rt_scene_cull_image(const rt_scene* s, int light_index, void* buf, size_t capacity, rt_cull_image_info* info) {
+    if (!s || !info) return fail(RT_ERR_INVALID_ARGUMENT, "rt_scene_cull_image: NULL argument");
+    if (light_index >= static_cast<int>(s->lights.size())) return fail(RT_ERR_INVALID_ARGUMENT, "rt_scene_cull_image: light %d of %zu", light_index, s->lights.size());
+    const int n = static_cast<int>(s->spheres.size());
+    const int n_pad = std::max(32, (n + 31) / 32 * 32), np = n_pad / 2;
+    double rot[9];
+    host::V3 Ln{0.f, 0.f, 0.f};
+    if (light_index >= 0) Ln = host::normalize3({s->lights[light_index].dir[0], s->lights[light_index].dir[1], s->lights[light_index].dir[2]});
+    light_frame(Ln, light_index >= 0, rot);
+    *info = rt_cull_image_info{};
+    info->bytes = static_cast<size_t>(np) * 32u + static_cast<size_t>(n_pad) * 16u;
+    info->n_spheres = n; info->n_pairs = np; info->off_B = np * 16; info->off_G = np * 32;
+    for (int k = 0; k < 9; ++k) info->rot[k] = static_cast<float>(rot[k]);
+    info->light_dir[0] = Ln.x; info->light_dir[1] = Ln.y; info->light_dir[2] = Ln.z;
+    if (buf) {
+        if (capacity < info->bytes) return fail(RT_ERR_INVALID_ARGUMENT, "rt_scene_cull_image: buffer of %zu bytes, image needs %zu", capacity, info->bytes);
+        unsigned char* b = static_cast<unsigned char*>(buf);
+        fill_pairs(s, np, rot, reinterpret_cast<float4*>(b), reinterpret_cast<float4*>(b + info->off_B));
+        fill_geom(s, n_pad, reinterpret_cast<float4*>(b + info->off_G));
     }
     return RT_OK;
 }

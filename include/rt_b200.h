@@ -203,6 +203,19 @@ RT_API int  rt_scene_accel_image(const rt_scene* scene, void* buf, size_t capaci
 /* Same with the finest group size to try (8, 16 or 32 slots; 0 = default), as rt_set_accel_group_slots sets it for a context. */
 RT_API int  rt_scene_accel_image_slots(const rt_scene* scene, int min_group_slots, void* buf, size_t capacity, rt_accel_image_info* info);
 
+/* ---- inspection: what the brute-force query stages (host only, needs no device) ----
+ * [0, off_B) float4 per pair (cx'0, cx'1, cy'0, cy'1); [off_B, off_G) float4 per pair (cz'0, cz'1, w0, w1); [off_G, bytes) float4 per
+ * sphere (cx, cy, cz, r) in world space.  c' = rot c: the centre in the light-aligned frame of light `light_index` (rows of rot =
+ * e1, e2, L; -1 = no light: identity), w = r^2 - |c|^2 + 2^-16 (|c|^2 + r^2); padding pairs have w = -1e30.  No counterpart in the
+ * reference (its BVH is what these arrays replace, ray-tracing.cpp:107-214); used by the CPU tests to model the conservative cull. */
+typedef struct rt_cull_image_info {
+    size_t  bytes;
+    int32_t n_spheres, n_pairs, off_B, off_G;
+    float   rot[9];
+    float   light_dir[3];      /* the normalised direction (light.cpp:7); 0 without a light */
+} rt_cull_image_info;
+RT_API int  rt_scene_cull_image(const rt_scene* scene, int light_index, void* buf, size_t capacity, rt_cull_image_info* info);
+
 /* ---- interop / instrumentation ---- */
 RT_API void* rt_hdr_device_ptr(rt_context* ctx);                   /* float4[W*H] in HBM (e.g. for an NCCL reduce) */
 RT_API int  rt_hdr_bind_external(rt_context* ctx, void* device_ptr); /* render into a caller-owned device buffer (NULL = own buffer) */

@@ -134,3 +134,69 @@ def test_filters_never_drop_what_the_exact_test_accepts(rt, which):
     assert np.all(tt[rr, g_of_slot[ss] // 8]), "an L2 box was skipped although the exact test accepts one of its spheres"
     # the boxes do filter: far fewer than all (ray, group) pairs are touched
     assert touched.mean() < 0.5
+
+
+# ---------------------------------------------------------------- brute force: the cull in the light-aligned frame (rt_device.cuh, SceneView)
+def _rot(m, v):
+    """rotate3(): fmaf(m0, x, fmaf(m1, y, m2 * z)) per row, binary32"""
+    x, y, z = v[:, 0], v[:, 1], v[:, 2]
+    return np.stack([fma(f32(m[3 * k]), x, fma(f32(m[3 * k + 1]), y, (f32(m[3 * k + 2]) * z).astype(f32))) for k in range(3)], 1)
+
+
+def shadow_cull_keeps(oq, cx, cy, cz, w):
+    """cull_pair<RAYS_SHADOW>: -c' as for the closest ray, b2 = o'z - c'z, sign of b2^2 - c'"""
+    ox, oy, oz = (oq[:, None, k] for k in range(3))
+    oo = fma(ox, ox, fma(oy, oy, (oz * oz).astype(f32)))
+    noo = fma(f32(2.0 ** -16), oo, -oo)
+    nc2 = (w[None] + noo).astype(f32)
+    nc2 = fma((oz + oz).astype(f32), cz[None], nc2); nc2 = fma((oy + oy).astype(f32), cy[None], nc2); nc2 = fma((ox + ox).astype(f32), cx[None], nc2)
+    b2 = fma(f32(-1.0), cz[None], oz)
+    return ~np.signbit(fma(b2, b2, nc2))
+
+
+@pytest.mark.parametrize("which,light", [("d488", 0), ("s4096", 0), ("random600", 0), ("three_lights", 1), ("three_lights", 2), ("d488", -1)])
+def test_light_aligned_cull_never_drops_what_the_exact_test_accepts(rt, which, light):
+    """The brute-force query culls in a rotated frame (third axis = the light direction) with coordinates rounded once to binary32 and
+    rays rotated in binary32 on the device; the exact test runs in world space.  Whatever Sphere::Intersect accepts -- for the
+    closest ray and for the shadow ray along L -- must survive the cull, and the arrays must be what the header says."""
+    if which == "random600":
+        scene = _random_flat_scene(rt, 21, 600, ground=True)
+        scene.add_light(rt.DirectionalLight((0.3, 0.9, -0.4), rt.XMCOLOR(1.0, 1.0, 1.0), 30000.0))      # the helper's scenes have no light
+    elif which == "three_lights":
+        scene = rt.scenes.scene_d488()
+        scene.add_light(rt.DirectionalLight((-1.0, 0.6, 0.2), rt.XMCOLOR(0.3, 0.5, 1.0), 25000.0))
+        scene.add_light(rt.DirectionalLight((1e-4, 0.0, -1.0), rt.XMCOLOR(1.0, 0.4, 0.3), 15000.0))
+    else:
+        scene = rt.scenes.NAMED[which]()
+    info, A, B, G = scene.cull_image(light)
+    n = info.n_spheres
+    rot = np.asarray(list(info.rot), np.float64)
+    R3 = rot.reshape(3, 3)
+    assert np.allclose(R3 @ R3.T, np.eye(3), atol=1e-6) and abs(np.linalg.det(R3) - 1.0) < 1e-5      # a rotation
+    Ld = np.asarray(list(info.light_dir), np.float64)
+    if light >= 0:
+        assert np.allclose(R3[2], Ld / np.linalg.norm(Ld), atol=1e-6)                                 # third axis = the light direction
+    cxq, cyq, czq = A[:, 0:2].reshape(-1)[:n], A[:, 2:4].reshape(-1)[:n], B[:, 0:2].reshape(-1)[:n]
+    w = B[:, 2:4].reshape(-1)[:n]
+    sp = scene.export().spheres
+    assert np.array_equal(G[:n, 0], sp["cx"]) and np.array_equal(G[:n, 1], sp["cy"]) and np.array_equal(G[:n, 2], sp["cz"]) and np.array_equal(G[:n, 3], sp["radius"])
+    cw = np.stack([sp["cx"], sp["cy"], sp["cz"]], 1).astype(np.float64)
+    assert np.allclose(np.stack([cxq, cyq, czq], 1), cw @ R3.T, rtol=0, atol=2e-7 * (1.0 + np.abs(cw).max()))   # c' = rot c, one rounding
+    r64 = sp["radius"].astype(np.float64)
+    cc = (cw * cw).sum(1)
+    assert np.allclose(w, r64 * r64 - cc + 2.0 ** -16 * (cc + r64 * r64), rtol=1e-6, atol=1e-6)
+    assert np.all(B[:, 2:4].reshape(-1)[n:] == f32(-1.0e30))                                           # padding never passes
+    rng = np.random.default_rng(5)
+    o, d = _rays(rng, cw, r64, 300 if which == "s4096" else 600)
+    cx, cy, cz, rad = (G[:n, k].copy() for k in range(4))
+    oq, dq = _rot(info.rot, o), _rot(info.rot, d)
+    acc = exact_accepts(o, d, cx, cy, cz, rad)
+    assert acc.sum() > 2 * len(o) // 3
+    assert not np.any(acc & ~cull_keeps(oq, dq, cxq, cyq, czq, w)), "the rotated-frame cull dropped a sphere the closest-hit test accepts"
+    if light >= 0:
+        Lf = np.broadcast_to(np.asarray(list(info.light_dir), f32), o.shape).copy()
+        accs = exact_accepts(o, Lf, cx, cy, cz, rad)
+        assert accs.sum() > len(o) // 10
+        assert not np.any(accs & ~shadow_cull_keeps(oq, cxq, cyq, czq, w)), "the rotated-frame cull dropped an occluder"
+        # and it does cull: most (ray, sphere) pairs are discarded
+        assert shadow_cull_keeps(oq, cxq, cyq, czq, w).mean() < 0.2
