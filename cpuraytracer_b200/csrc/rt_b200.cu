@@ -1067,7 +1067,8 @@ int rt_render(rt_context* c, uint64_t first_sample, int spp, int max_depth, uint
 // (different streams / contexts on one device) race on it.
 // ------------------------------------------------------------------------------------------------
 static __device__ __align__(256) unsigned char g_static_scratch[RT_STATIC_SCRATCH_BYTES];
-static unsigned char* g_static_scratch_ptr[64];          // per device: the array's DEVICE address (the symbol itself is a host-side stand-in)
+static unsigned char* g_static_scratch_ptr[64];          // per device: the array's DEVICE address (the symbol itself is a host-side stand-in).
+                                                         // Two host threads racing through the first call on a device store the same value.
 static int static_scratch_of_current_device(int device, unsigned char** out) {
     if (device < 0 || device >= 64) return fail(RT_ERR_UNSUPPORTED, "rt_render_static: device %d out of the supported range [0,64)", device);
     if (!g_static_scratch_ptr[device]) {                 // once per device, with that device current (ctx_use ran)

@@ -227,6 +227,13 @@ public:
         m_sampleCount += static_cast<uint64_t>(spp);
         return static_cast<size_t>(m_w) * m_h * static_cast<size_t>(spp);
     }
+    // The same render without a single allocation (scratch in the library's static device array; rt_b200.h: rt_render_static -- no
+    // counterpart in the reference).  Throws rtb200::Error(RT_ERR_UNSUPPORTED) when the job does not fit the array.
+    size_t RenderStatic(int spp, int maxDepth, uint32_t flags = 0) {
+        check(rt_render_static(m_ctx, m_sampleCount + 1, spp, maxDepth, flags));
+        m_sampleCount += static_cast<uint64_t>(spp);
+        return static_cast<size_t>(m_w) * m_h * static_cast<size_t>(spp);
+    }
     void Synchronize() { check(rt_synchronize(m_ctx)); }
 
     std::vector<float> ReadHdrSum() {                                // m_backbufferHdr: float4 running sum, w = samples
