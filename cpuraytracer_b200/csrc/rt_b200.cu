@@ -943,6 +943,9 @@ static int render_one_kernel(rt_context* c, rt::RenderParams& p, int spp, uint32
 #ifndef RT_LADDER_GRAN
 #define RT_LADDER_GRAN 8
 #endif
+#ifndef RT_BATCH_CAP_PIXELS
+#define RT_BATCH_CAP_PIXELS (4u << 20)
+#endif
 #ifndef RT_BATCH_CAP_MIB
 #define RT_BATCH_CAP_MIB 512   /* first-hit records of one batch of an image up to 4 Mpixel (larger images: 256 MiB or two running-sum buffers) */
 #endif
@@ -966,7 +969,7 @@ static int render_two_stage(rt_context* c, rt::RenderParams& p, int spp, int max
     // buffers, whichever is more), a multiple of 16, at most 4096: 128 frames at 1920x1080, 16 at 3840x2160 -- the records are the only
     // per-batch allocation
     // (measured at 1920x1080, 256 frames per call: 64 / 128 / 256 frames per batch = 295.5 / 289.9 / 292.5 ms -- profiles/r02/r02x_batch_size_probe.txt)
-    const size_t cap_bytes = n_pix <= (4u << 20) ? (static_cast<size_t>(RT_BATCH_CAP_MIB) << 20) : std::max<size_t>(256ull << 20, n_pix * 32);
+    const size_t cap_bytes = n_pix <= RT_BATCH_CAP_PIXELS ? (static_cast<size_t>(RT_BATCH_CAP_MIB) << 20) : std::max<size_t>(256ull << 20, n_pix * 32);
     int batch = static_cast<int>(std::min<size_t>(4096, std::max<size_t>(16, (cap_bytes / (n_pix * 2)) & ~static_cast<size_t>(15))));
     batch = std::min(batch, (spp + 15) & ~15);
     const size_t hits_need = n_pix * static_cast<size_t>(batch) * sizeof(uint16_t);

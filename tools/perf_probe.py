@@ -9,6 +9,9 @@ import cpuraytracer_b200 as rt
 FLAGS = int(os.environ.get("RT_PROBE_FLAGS", "0"), 0)     # e.g. 4 = RT_FLAG_WAVEFRONT
 
 CASES = [("d488", 1920, 1080, 64, 50), ("d488", 1920, 1080, 64, 0), ("s4096", 1920, 1080, 8, 50)]
+if os.environ.get("RT_PROBE_RES"):                       # e.g. 3840x2160
+    rw, rh = (int(v) for v in os.environ["RT_PROBE_RES"].split("x"))
+    CASES = [(n, rw, rh, s, d) for n, _, _, s, d in CASES]
 if os.environ.get("RT_PROBE_SPP"):                       # e.g. 256: the default bench step (several batches per call)
     CASES = [(n, w, h, int(os.environ["RT_PROBE_SPP"]) // (8 if n == "s4096" else 1), d) for n, w, h, _, d in CASES]
 if len(sys.argv) > 1:
