@@ -261,6 +261,43 @@ def short_config_runs(rt, local, flush, skip):
     return out
 
 
+def static_entry_run(rt, local, workload, flush):
+    """rt_render_static (the entry point that allocates nothing: scratch in the library's static device array) on the bench workload:
+    1 warm-up + 2 timed calls of 64 frames, checked against rt_render on the same frames.  None where the job does not fit the array."""
+    import numpy as np
+    import torch
+    scene_name, w, h, depth, _, _ = WORKLOADS[workload]
+    spp = 64
+    if rt.load().rt_render_static_scratch_bytes(w, h, spp) > rt._lib.RT_STATIC_SCRATCH_BYTES:
+        return None
+    r = rt.Renderer(device=local, width=w, height=h, stream=torch.cuda.current_stream(local).cuda_stream)
+    r.set_scene(rt.scenes.NAMED[scene_name]())
+    r.set_camera(rt.scenes.default_camera(aspect=w / h))
+    r.render_static(spp, depth, 0, first_sample=1)
+    torch.cuda.synchronize()
+    r.clear()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(2)]
+    for i in range(2):
+        flush.fill_(i)
+        ev[i][0].record()
+        r.render_static(spp, depth, 0, first_sample=1 + i * spp)
+        ev[i][1].record()
+    torch.cuda.synchronize()
+    ms = sum(a.elapsed_time(b) for a, b in ev)
+    got = r.read_hdr_sum()
+    r.clear()
+    r.set_chunk_spp(1 << 20)                                  # rt_render with one work item per pixel and batch: the same sequential sums
+    r.render(2 * spp, depth, 0, first_sample=1)
+    ref = r.read_hdr_sum()
+    r.close()
+    a, b = got[..., :3].astype(np.float64), ref[..., :3].astype(np.float64)
+    rel = float(np.max(np.abs(a - b) / np.maximum(np.abs(b), 1e-3 * b.mean())))
+    assert np.array_equal(got[..., 3], ref[..., 3]) and rel < 2e-4, rel
+    return {"entry_point": "rt_render_static (no allocation per call; scratch = 64 MiB static device array; batches of 16 frames)",
+            "value": 2 * spp * w * h / (ms * 1e-3), "unit": "path samples/s", "spp_per_call": spp, "calls": 2,
+            "max_rel_diff_vs_rt_render": rel, "bitwise_equal_to_rt_render": bool(np.array_equal(got, ref))}
+
+
 def rmse_vs_golden(rt, local):
     """BASELINE.json's metric names "RMSE vs CPU ref": per config the GPU's converged linear radiance against the committed golden
     of the reference's own renderer (tests/golden/golden_converged.npz: oracle/_ref at 65,536 spp, 240x135), same spp on the GPU.
@@ -443,6 +480,7 @@ def run_b200(args):
     parity_n = parity_across_gpus(rt, ShardedRenderer, scene, depth, world, rank, local) if world > 1 else None
     extra_configs = short_config_runs(rt, local, flush, args.workload) if (world == 1 and rank == 0 and not args.no_extras) else None
     rmse = rmse_vs_golden(rt, local) if (rank == 0 and not args.no_extras) else None
+    static_entry = static_entry_run(rt, local, args.workload, flush) if (world == 1 and rank == 0 and not args.no_extras) else None
 
     if rank == 0:
         kern_s = float(kern_ms.item()) * 1e-3
@@ -477,6 +515,8 @@ def run_b200(args):
             line["configs"] = extra_configs
         if rmse:
             line["rmse"] = rmse
+        if static_entry:
+            line["static_entry"] = static_entry
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(args.workload, args.cpu_seconds)
         _emit(line)
